@@ -1,0 +1,115 @@
+"""CPU: pins the plain-C restatement (oracle/eri_oracle.c) against what the reference's own compiled
+extension produced (tests/golden/*.npz, made by oracle/make_golden.py), and -- when oracle/_ref is
+present (build container) -- against the live reference on a fresh seeded case."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from quemb_b200 import indexing, synthetic as syn
+
+from helpers import CASES, Golden
+
+TOL = 1e-10  # max-abs on (ij|kl); BASELINE.json north_star
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_index_maps_bit_exact(name):
+    g = Golden(name)
+    rptr, ridx, rcol, uptr, uidx = oracle.reachable_columns(g.exch)
+    assert oracle.from_csr(uptr, uidx) == [u.tolist() for u in g.uniq]
+    # every key the reference assigned has the same column here
+    for mu, lst in enumerate(g.exch):
+        for k, nu in enumerate(lst):
+            key = oracle.ravel_symmetric(mu, int(nu))
+            assert rcol[rptr[mu] + k] == g.offsets.get(key, 0)
+    # python host twins agree as well
+    uniq = indexing.extract_unique(g.exch)
+    assert uniq == [u.tolist() for u in g.uniq]
+    off = indexing.unique_offsets(uniq)
+    assert {k: v for k, v in g.offsets.items() if k in off} == off
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_steps_match_reference_golden(name):
+    g = Golden(name)
+    for f in range(g.n_frag):
+        fr = g.frag(f)
+        A = oracle.get_AO_per_MO(fr["TA"], g.S_abs, g.eps)
+        assert [a.tolist() for a in A] == [a.tolist() for a in fr["A"]], "AO_by_MO pattern must be bit-exact"
+        B = oracle.contract_with_TA_1st(fr["TA"], g.M, g.exch, A)
+        assert B.shape == fr["B"].shape
+        assert np.abs(B - fr["B"]).max() <= 1e-12
+        sym = oracle.contract_with_TA_2nd_to_sym_dense(B, fr["TA"], A)
+        assert np.abs(sym - fr["sym"]).max() <= 1e-12
+        G = oracle.transform_integral(g.M, g.exch, fr["TA"], g.S_abs, g.L, g.eps)
+        assert G.shape == fr["G"].shape
+        assert np.abs(G - fr["G"]).max() <= TOL
+        assert np.array_equal(G, G.T)
+
+
+def test_k2a_uses_lists_of_min_and_TA_of_max():
+    """eri_sparse_DF.cpp:595 + indexers.hpp:95: with coarse screening the other convention is off by O(eps)."""
+    g = Golden("coarse_eps")
+    fr = g.frag(0)
+    TA, A, B = fr["TA"], fr["A"], fr["B"]
+    nmo = TA.shape[1]
+    aptr, _ = oracle.to_csr(A)
+    wrong = np.zeros_like(fr["sym"])
+    for hi in range(nmo):
+        for lo in range(hi + 1):
+            col = indexing.ravel_symmetric(hi, lo)
+            for k, mu in enumerate(A[hi]):  # lists of MAX (wrong)
+                wrong[:, col] += TA[mu, lo] * B[:, aptr[hi] + k]
+    assert np.abs(wrong - fr["sym"]).max() > 1e-6
+
+
+def test_reference_indexing_golden(golden_dir):
+    """tests/test_indexing.py:4-11 of the reference: unravel(ravel(a,b,c,d)) round trip, n = 10."""
+    abcd = np.load(golden_dir / "indexing_n10.npz")["abcd"]
+    for a, b, c, d in abcd.tolist():
+        assert indexing.unravel_eri_idx(indexing.ravel_eri_idx(a, b, c, d)) == (a, b, c, d)
+    for i in range(5000):
+        assert oracle.unravel_symmetric(i) == indexing.unravel_symmetric(i)
+        lo, hi = indexing.unravel_symmetric(i)
+        assert lo <= hi and indexing.ravel_symmetric(lo, hi) == i == oracle.ravel_symmetric(hi, lo)
+
+
+def test_dense_restatement_unscreened():
+    """With complete lists the path equals the dense einsum / solve_triangular restatement."""
+    from scipy.linalg import solve_triangular
+
+    p = syn.make_chain_problem(n_units=3, ao_per_unit=3, n_end=0, naux=12, frag_halfwidth=0, n_bath=3,
+                               sigma=5.0, cond=1e3, seed=5)
+    nao = p.nao
+    assert all(len(x) == nao for x in p.exch_reachable)
+    mus, nus = syn.unique_pairs(p.exch_reachable)
+    dense = np.zeros((p.naux, nao, nao))
+    dense[:, mus, nus] = p.unique_dense_data
+    dense[:, nus, mus] = p.unique_dense_data
+    TA = p.TAs[1]
+    nmo = TA.shape[1]
+    Pij = np.einsum("Pmn,mi,nj->Pij", dense, TA, TA)
+    sym = np.zeros((p.naux, nmo * (nmo + 1) // 2))
+    for i in range(nmo):
+        for j in range(i + 1):
+            sym[:, indexing.ravel_symmetric(i, j)] = Pij[:, i, j]
+    X = solve_triangular(p.L_PQ, sym, lower=True)
+    G = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, np.ones((nao, nao)), p.L_PQ, 1e-5)
+    assert np.abs(G - X.T @ X).max() <= 1e-11
+
+
+def test_live_reference_if_present():
+    ref = oracle.reference_module()
+    if ref is None:
+        pytest.skip("oracle/_ref not built on this box")
+    p = syn.make_chain_problem(n_units=7, ao_per_unit=4, n_end=1, naux=32, frag_halfwidth=1, n_bath=5,
+                               sigma=0.5, seed=77)
+    T = ref.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao),
+                                  [x.tolist() for x in p.exch_reachable])
+    for TA in p.TAs[:3]:
+        Gref = ref.transform_integral(T, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+        G = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ,
+                                      p.MO_coeff_epsilon)
+        assert np.abs(G - Gref).max() <= TOL
