@@ -1,0 +1,174 @@
+/*
+ * qemb_b200.h -- C ABI of libqemb_b200.so: the B200-native (sm_100a, FP64) sparse-DF fragment ERI
+ * transform that replaces QuEmb's Eigen extension `quemb.molbe._cpp.eri_sparse_DF`.
+ *
+ * Every entry point names the reference interface it stands in for
+ * ("cpp:" = src/quemb/molbe/_cpp/eri_sparse_DF.cpp, "hpp:" = .../indexers.hpp,
+ *  "pyi:" = .../eri_sparse_DF.pyi, "py:" = src/quemb/molbe/eri_sparse_DF.py of troyvvgroup/quemb).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ / torch types cross this boundary.
+ *   - every function returns 0 on success, a negative QEMB_E* code on failure; the message of the
+ *     last failure on the calling thread is returned by qemb_last_error().  Nothing throws.
+ *   - all host matrices are column-major FP64 (the reference's Eigen default, cpp:29-33) with an
+ *     explicit leading dimension; index lists are CSR pairs (ptr[n+1], idx[nnz]) of int64
+ *     (hpp:16-17).
+ *   - "dev" pointers are CUDA device pointers of the handle's device; "host" pointers may be pageable
+ *     or pinned (pinned makes the copies asynchronous).
+ *   - handles are immutable after upload and may be shared by concurrent qemb_fragment_* calls that
+ *     use different qemb_workspace objects (the reference releases the GIL around every call,
+ *     cpp:889-938).
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry point fails with
+ *     QEMB_ENODEV.
+ */
+#ifndef QEMB_B200_H
+#define QEMB_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QEMB_OK 0
+#define QEMB_EINVAL (-1)  /* bad argument / shape mismatch  (std::runtime_error, cpp:228-238)      */
+#define QEMB_ENOMEM (-2)  /* device or host allocation failed (std::bad_alloc, cpp:56-62)          */
+#define QEMB_ECUDA (-3)   /* CUDA runtime error               (CUDA_CHECK_THROW, cpp:40-46)        */
+#define QEMB_ENODEV (-4)  /* no CUDA device                                                         */
+#define QEMB_EINDEX (-5)  /* (mu,nu) not in the screened set  (std::out_of_range, cpp:210)         */
+
+typedef struct qemb_ctx qemb_ctx;             /* one CUDA device + stream                           */
+typedef struct qemb_tensor qemb_tensor;       /* SemiSparseSym3DTensor on the device, cpp:110-298   */
+typedef struct qemb_metric qemb_metric;       /* GPU_MatrixHandle, cpp:64-107                       */
+typedef struct qemb_screen qemb_screen;       /* S_abs on the device (input of cpp:443-465)         */
+typedef struct qemb_workspace qemb_workspace; /* per-caller scratch: plan, B, X, G buffers          */
+
+const char *qemb_last_error(void);
+const char *qemb_version(void);
+
+/* -- device -------------------------------------------------------------------------------------- */
+int qemb_device_count(int *n);
+int qemb_ctx_create(int device, qemb_ctx **out);
+void qemb_ctx_destroy(qemb_ctx *);
+int qemb_ctx_synchronize(qemb_ctx *);
+int qemb_ctx_device(const qemb_ctx *, int *device);
+
+/* -- index maps (host, exact integer arithmetic) ------------------------------------------------- */
+/* hpp:75-79 */
+int64_t qemb_ravel_symmetric(int64_t a, int64_t b);
+/* hpp:89-96; returns (min,max) like the C++ reference (exact integer arithmetic, no double sqrt) */
+void qemb_unravel_symmetric(int64_t i, int64_t *lo, int64_t *hi);
+/* extract_unique, hpp:149-162 / pyi:132: prefix nu<=mu of every sorted list.
+ * uniq_ptr has nao+1 entries; uniq_idx may be NULL to count only. Returns n_unique (or <0). */
+int64_t qemb_extract_unique(int64_t nao, const int64_t *exch_ptr, const int64_t *exch_idx,
+                            int64_t *uniq_ptr, int64_t *uniq_idx);
+
+/* -- SemiSparseSym3DTensor: screened (P|mu nu) ---------------------------------------------------- */
+/* ctor #3, cpp:143-164 (+ compute_offsets_and_unique cpp:248-258,
+ * initialize_exch_reachable_with_offsets cpp:260-279).  Allocates naux x n_unique on the device
+ * (NaN-filled like cpp:160) and builds the column maps. exch lists must be sorted ascending. */
+int qemb_tensor_create(qemb_ctx *, int64_t naux, int64_t nao, const int64_t *exch_ptr,
+                       const int64_t *exch_idx, qemb_tensor **out);
+void qemb_tensor_destroy(qemb_tensor *);
+int qemb_tensor_n_unique(const qemb_tensor *, int64_t *n_unique);
+/* nonzero_size / size, cpp:196-201 */
+int qemb_tensor_shape(const qemb_tensor *, int64_t *naux, int64_t *nao, int64_t *n_unique);
+/* column of the pair (mu,nu) (= offsets[ravel_symmetric(mu,nu)], cpp:210); QEMB_EINDEX if unscreened */
+int qemb_tensor_column(const qemb_tensor *, int64_t mu, int64_t nu, int64_t *col);
+/* exch_reachable_with_offsets, cpp:260-279: col[k] for every entry k of the full exch lists
+ * (a pair whose key was never assigned reads column 0, the reference's operator[] default). */
+int qemb_tensor_reachable_columns(const qemb_tensor *, int64_t *col /* nnz(exch) */);
+/* fills columns [col0, col0+ncols) from host (replaces writes through mut_unique_dense_data,
+ * cpp:810-812, py:486-488) */
+int qemb_tensor_upload(qemb_tensor *, const double *host, int64_t ld_host, int64_t col0, int64_t ncols);
+/* reads columns back (unique_dense_data / __getitem__, cpp:203-215, 806-826) */
+int qemb_tensor_download(const qemb_tensor *, double *host, int64_t ld_host, int64_t col0, int64_t ncols);
+
+/* -- Coulomb metric ------------------------------------------------------------------------------- */
+/* GPU_MatrixHandle(L_host), cpp:64-107 / pyi:29-36: lower Cholesky factor of (P|Q), column-major.
+ * Also inverts the diagonal blocks once (used by the blocked DMMA triangular solve). */
+int qemb_metric_create(qemb_ctx *, const double *L_host, int64_t ld, int64_t naux, qemb_metric **out);
+void qemb_metric_destroy(qemb_metric *);
+
+/* Optional (design option O1): W = L^-1 (P|mu nu) once for the whole molecule, in place on the
+ * device copy; afterwards qemb_fragment_transform skips the per-fragment solve (cpp:615). */
+int qemb_tensor_whiten(qemb_tensor *, const qemb_metric *);
+int qemb_tensor_is_whitened(const qemb_tensor *, int *flag);
+
+/* -- screening input ------------------------------------------------------------------------------ */
+int qemb_screen_create(qemb_ctx *, const double *S_abs_host, int64_t ld, int64_t nao, qemb_screen **out);
+void qemb_screen_destroy(qemb_screen *);
+
+/* -- per-caller workspace -------------------------------------------------------------------------- */
+int qemb_workspace_create(qemb_ctx *, qemb_workspace **out);
+void qemb_workspace_destroy(qemb_workspace *);
+/* bytes currently held on the device by this workspace */
+int qemb_workspace_bytes(const qemb_workspace *, int64_t *bytes);
+
+/* -- the fragment path ----------------------------------------------------------------------------- */
+/* get_AO_per_MO, cpp:443-465 / pyi:137: X = |S_abs * TA| on the device (plain left-to-right FP64
+ * sums, no FMA contraction), A(i) = {mu : X(mu,i) >= eps}.  Stores the lists in the workspace
+ * ("the plan") and returns the total count.  TA is nao x nmo column-major on the host. */
+int qemb_fragment_screen(qemb_workspace *, const qemb_screen *, const double *TA_host, int64_t ld,
+                         int64_t nao, int64_t nmo, double eps, int64_t *n_mu_i);
+/* plan from caller-supplied lists (the AO_by_MO argument of contract_with_TA_1st, pyi:126) */
+int qemb_fragment_set_lists(qemb_workspace *, const double *TA_host, int64_t ld, int64_t nao,
+                            int64_t nmo, const int64_t *A_ptr, const int64_t *A_idx);
+/* read the plan's lists back: A_ptr[nmo+1], A_idx[n_mu_i] */
+int qemb_fragment_get_lists(const qemb_workspace *, int64_t *A_ptr, int64_t *A_idx);
+
+/* K1, contract_with_TA_1st cpp:484-532: B[:, off(i,mu)] = sum_{nu in R(mu)} TA(nu,i) M[:, col(mu,nu)],
+ * column offsets = running counter over i then mu in A(i) (cpp:467-482).  Result stays on the device
+ * inside the workspace. */
+int qemb_fragment_contract_1st(qemb_workspace *, const qemb_tensor *);
+/* K2a, contract_with_TA_2nd_to_sym_dense cpp:560-605: sym[:, T(hi)+lo] = sum_{mu in A(lo)} TA(mu,hi) B[:, off(lo,mu)] */
+int qemb_fragment_contract_2nd(qemb_workspace *);
+/* K2b, eval_via_cholesky step 1 cpp:615: X = L^-1 sym (in place in the workspace) */
+int qemb_fragment_solve(qemb_workspace *, const qemb_metric *);
+/* K3, eval_via_cholesky step 2 cpp:620: G = X^T X, full npair x npair square, symmetric, s4 pair
+ * order ij = T(max)+min.  Output stays in the workspace. */
+int qemb_fragment_gram(qemb_workspace *);
+
+/* debugging / parity taps: copy intermediates of the last fragment to the host (column-major) */
+int qemb_fragment_get_B(const qemb_workspace *, double *host, int64_t ld);   /* naux x n_mu_i   */
+int qemb_fragment_get_sym(const qemb_workspace *, double *host, int64_t ld); /* naux x npair    */
+int qemb_fragment_get_G(const qemb_workspace *, double *host, int64_t ld);   /* npair x npair   */
+/* device address of G (npair x npair, ld = npair) for zero-copy consumers (e.g. NCCL reduce) */
+int qemb_fragment_G_dev(const qemb_workspace *, void **dev, int64_t *npair);
+
+/* transform_integral / transform_integral_cuda, cpp:724-751 / pyi:158-181: screen -> K1 -> K2a ->
+ * (K2b unless the tensor is whitened) -> K3 for one fragment.
+ *   out         npair x npair FP64, ld_out >= npair.  Host pointer unless out_is_device != 0.
+ *   p_begin/end restrict the auxiliary index to [p_begin, p_end) (aux-sharded fragments; requires a
+ *               whitened tensor; pass 0, -1 for the full range).  The result is then the PARTIAL
+ *               Gram matrix of that slab, to be summed over ranks.
+ * The call is asynchronous on the ctx stream when `out` is pinned or device memory;
+ * qemb_ctx_synchronize() completes it. */
+int qemb_fragment_transform(qemb_workspace *, const qemb_tensor *, const qemb_metric *,
+                            const qemb_screen *, const double *TA_host, int64_t ld, int64_t nao,
+                            int64_t nmo, double eps, int64_t p_begin, int64_t p_end, double *out,
+                            int64_t ld_out, int out_is_device);
+
+/* Algorithmic work of the last planned fragment (SURVEY 8d formulas): flops and bytes of K1, K2a,
+ * K2b, K3 in that order (8 doubles). */
+int qemb_fragment_work(const qemb_workspace *, const qemb_tensor *, double *flops_bytes8);
+/* device time in ms of the kernels of the last fragment: screen, K1, K2a, K2b, K3 (CUDA events on
+ * the ctx stream; only recorded when enabled) */
+int qemb_ctx_set_timing(qemb_ctx *, int enabled);
+int qemb_fragment_times(const qemb_workspace *, float *ms5);
+/* number of kernel launches issued by this library on this ctx since creation */
+int qemb_ctx_launch_count(const qemb_ctx *, int64_t *n);
+
+/* pinned host memory helpers (so that Python callers can hand out asynchronous buffers) */
+int qemb_host_alloc(void **p, int64_t bytes);
+int qemb_host_free(void *p);
+
+/* FP64 DGEMM-shaped peak probe: runs the library's own DMMA mainloop on an n x n x k problem that
+ * lives entirely in L2/smem and returns TFLOP/s (used to report the tensor-pipe ceiling next to
+ * the cuBLAS figure). */
+int qemb_probe_dmma_tflops(qemb_ctx *, int64_t n, int64_t k, int iters, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QEMB_B200_H */

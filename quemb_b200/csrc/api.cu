@@ -1,0 +1,1308 @@
+// api.cu -- host side of libqemb_b200: handles, index maps, per-fragment plans and the C ABI declared in
+// include/qemb_b200.h.  Reference citations: "cpp:" = src/quemb/molbe/_cpp/eri_sparse_DF.cpp,
+// "hpp:" = src/quemb/molbe/_cpp/indexers.hpp of troyvvgroup/quemb.
+//
+// Streams per context:
+//   compute  K1, K2a, K2b, K3 of consecutive fragments, in order
+//   prep     TA upload, screening kernel, mask download, plan upload of the NEXT fragment
+//   copy     device -> host copy of a finished G while the next fragment computes
+// Fragment-local inputs (TA, mask, plan tables) are double buffered ("slots"), and so is G when it has
+// to travel to the host, so that back-to-back qemb_fragment_transform calls pipeline without any
+// host-side wait on the compute stream.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/qemb_b200.h"
+#include "common.cuh"
+#include "kernels.cuh"
+
+using namespace qemb;
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string &msg)
+{
+    g_err = msg;
+    return code;
+}
+#define CU(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e__ = (call);                                                                       \
+        if (e__ != cudaSuccess) {                                                                       \
+            const int code__ = (e__ == cudaErrorMemoryAllocation) ? QEMB_ENOMEM                         \
+                               : (e__ == cudaErrorNoDevice || e__ == cudaErrorInsufficientDriver)       \
+                                   ? QEMB_ENODEV                                                        \
+                                   : QEMB_ECUDA;                                                        \
+            return fail(code__, std::string(#call) + ": " + cudaGetErrorString(e__));                   \
+        }                                                                                               \
+    } while (0)
+#define REQ(cond, msg)                                                                                  \
+    do {                                                                                                \
+        if (!(cond)) return fail(QEMB_EINVAL, std::string(msg) + " [" #cond "]");                       \
+    } while (0)
+#define TRY(expr)                                                                                       \
+    do {                                                                                                \
+        int rc__ = (expr);                                                                              \
+        if (rc__ != QEMB_OK) return rc__;                                                               \
+    } while (0)
+
+extern "C" const char *qemb_last_error(void) { return g_err.c_str(); }
+extern "C" const char *qemb_version(void) { return "quemb-b200 0.1 (sm_100a, FP64 DMMA)"; }
+
+// ------------------------------------------------------------------------------------------------
+// handles
+// ------------------------------------------------------------------------------------------------
+struct qemb_ctx {
+    int device = 0;
+    cudaStream_t compute = nullptr, prep = nullptr, copy = nullptr;
+    bool timing = false;
+    int64_t launches = 0;
+};
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes)
+    {
+        if (bytes <= cap) return QEMB_OK;
+        if (p) {
+            CU(cudaFree(p));
+            p = nullptr;
+            cap = 0;
+        }
+        const size_t want = bytes + bytes / 16;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            e = cudaMalloc(&p, bytes);
+            if (e != cudaSuccess) {
+                (void)cudaGetLastError();
+                p = nullptr;
+                return fail(QEMB_ENOMEM, "cudaMalloc of " + std::to_string(bytes) + " bytes failed");
+            }
+            cap = bytes;
+        } else {
+            cap = want;
+        }
+        return QEMB_OK;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T *as() const
+    {
+        return static_cast<T *>(p);
+    }
+};
+
+struct HostBuf { // pinned
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes)
+    {
+        if (bytes <= cap) return QEMB_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        const size_t want = bytes + bytes / 4 + 4096;
+        CU(cudaMallocHost(&p, want));
+        cap = want;
+        return QEMB_OK;
+    }
+    void release()
+    {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+inline int64_t gauss_sum(int64_t n) { return n * (n + 1) / 2; }
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev)
+    {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard()
+    {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+} // namespace
+
+struct qemb_tensor {
+    qemb_ctx *ctx = nullptr;
+    int64_t naux = 0, nao = 0, n_unique = 0;
+    int64_t ldp = 0;    // leading dimension on the device: naux rounded up to 128, pad rows zero
+    int64_t naux16 = 0; // naux rounded up to 16: rows the kernels touch
+    std::vector<int64_t> rptr, ridx, rcol; // exch_reachable lists + column of every entry (cpp:260-279)
+    std::vector<int64_t> uptr, uidx;       // exch_reachable_unique (hpp:149-162)
+    DevBuf data, d_rcol, d_ridx;           // FP64 ldp x n_unique ; int32 copies of rcol / ridx
+    bool whitened = false;
+};
+
+struct qemb_metric {
+    qemb_ctx *ctx = nullptr;
+    int64_t naux = 0, naux_pad = 0;
+    int nblocks = 0;
+    DevBuf L, Dinv;
+};
+
+struct qemb_screen {
+    qemb_ctx *ctx = nullptr;
+    int64_t nao = 0;
+    DevBuf S;
+};
+
+namespace {
+
+struct PlanDev { // device pointers into a slot's plan buffer
+    const int *bcol1 = nullptr, *ccol1 = nullptr;
+    const GatherGroup *groups1 = nullptr;
+    const int4 *tiles1 = nullptr;
+    int ntiles1 = 0;
+    const int *acol2 = nullptr, *brow2 = nullptr, *bcol2 = nullptr, *ccol2 = nullptr;
+    const GatherGroup *groups2 = nullptr;
+    const int4 *tiles2 = nullptr;
+    int ntiles2 = 0;
+};
+
+struct Slot {
+    int64_t nao = 0, nmo = 0, npair = 0, nA = 0;
+    std::vector<int64_t> aptr, aidx;
+    DevBuf TA, mask, plan1, plan2;
+    HostBuf stage1, stage2, hmask;
+    PlanDev pd;
+    cudaEvent_t uploaded1 = nullptr, uploaded2 = nullptr, consumed = nullptr, ta_ready = nullptr;
+    bool consumed_pending = false;
+    bool have_plan1 = false, have_plan2 = false;
+    const qemb_tensor *plan1_tensor = nullptr;
+    double work[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
+} // namespace
+
+struct qemb_workspace {
+    qemb_ctx *ctx = nullptr;
+    Slot slot[2];
+    int cur = 0;
+    bool started = false;
+    // intermediates of the current fragment (compute stream order protects them)
+    DevBuf Bint, sym;
+    int64_t ldp = 0, mrows = 0; // leading dimension / valid rows of Bint and sym for the current fragment
+    int64_t naux = 0;
+    bool have_B = false, have_sym = false, solved = false;
+    // G
+    DevBuf G[2];
+    cudaEvent_t g_copied[2] = {nullptr, nullptr};
+    bool g_copy_pending[2] = {false, false};
+    int gi = 0;
+    double *G_last = nullptr; // where the last K3 wrote
+    int64_t G_last_ld = 0;
+    bool have_G = false;
+    // gram tile lists by number of row tiles
+    std::map<int, std::pair<DevBuf, int>> gram_tiles;
+    // timing
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evs[2] = {nullptr, nullptr};
+    bool ev_valid[5] = {false, false, false, false, false};
+    bool evs_valid = false;
+};
+
+// ------------------------------------------------------------------------------------------------
+// device / ctx
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_device_count(int *n)
+{
+    REQ(n != nullptr, "null output");
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        *n = 0;
+        return fail(QEMB_ENODEV, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+    }
+    *n = c;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_create(int device, qemb_ctx **out)
+{
+    REQ(out != nullptr, "null output");
+    *out = nullptr;
+    int n = 0;
+    TRY(qemb_device_count(&n));
+    if (n <= 0) return fail(QEMB_ENODEV, "no CUDA device visible: libqemb_b200 has no CPU fallback");
+    REQ(device >= 0 && device < n, "device index out of range");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(QEMB_ENODEV, std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                                     std::to_string(prop.minor) + "; this library is built for sm_100a only");
+    qemb_ctx *c = new (std::nothrow) qemb_ctx;
+    if (!c) return fail(QEMB_ENOMEM, "host allocation failed");
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->prep, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
+    *out = c;
+    return QEMB_OK;
+}
+
+extern "C" void qemb_ctx_destroy(qemb_ctx *c)
+{
+    if (!c) return;
+    DeviceGuard g(c->device);
+    cudaStreamSynchronize(c->compute);
+    cudaStreamSynchronize(c->prep);
+    cudaStreamSynchronize(c->copy);
+    cudaStreamDestroy(c->compute);
+    cudaStreamDestroy(c->prep);
+    cudaStreamDestroy(c->copy);
+    delete c;
+}
+
+extern "C" int qemb_ctx_synchronize(qemb_ctx *c)
+{
+    REQ(c != nullptr, "null ctx");
+    DeviceGuard g(c->device);
+    CU(cudaStreamSynchronize(c->prep));
+    CU(cudaStreamSynchronize(c->compute));
+    CU(cudaStreamSynchronize(c->copy));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_device(const qemb_ctx *c, int *device)
+{
+    REQ(c != nullptr && device != nullptr, "null argument");
+    *device = c->device;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_set_timing(qemb_ctx *c, int enabled)
+{
+    REQ(c != nullptr, "null ctx");
+    c->timing = enabled != 0;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_launch_count(const qemb_ctx *c, int64_t *n)
+{
+    REQ(c != nullptr && n != nullptr, "null argument");
+    *n = c->launches;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_host_alloc(void **p, int64_t bytes)
+{
+    REQ(p != nullptr && bytes >= 0, "bad argument");
+    *p = nullptr;
+    if (bytes == 0) return QEMB_OK;
+    cudaError_t e = cudaMallocHost(p, (size_t)bytes);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(QEMB_ENOMEM, std::string("cudaMallocHost: ") + cudaGetErrorString(e));
+    }
+    return QEMB_OK;
+}
+extern "C" int qemb_host_free(void *p)
+{
+    if (p) CU(cudaFreeHost(p));
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// index maps
+// ------------------------------------------------------------------------------------------------
+extern "C" int64_t qemb_ravel_symmetric(int64_t a, int64_t b)
+{
+    return (a > b) ? gauss_sum(a) + b : gauss_sum(b) + a;
+}
+
+extern "C" void qemb_unravel_symmetric(int64_t I, int64_t *lo, int64_t *hi)
+{
+    // largest a with a(a+1)/2 <= I, exact: start from the floating estimate and correct
+    int64_t a = (int64_t)((std::sqrt(8.0 * (double)I + 1.0) - 1.0) / 2.0);
+    while (gauss_sum(a) > I) --a;
+    while (gauss_sum(a + 1) <= I) ++a;
+    const int64_t b = I - gauss_sum(a);
+    if (a <= b) {
+        *lo = a;
+        *hi = b;
+    } else {
+        *lo = b;
+        *hi = a;
+    }
+}
+
+extern "C" int64_t qemb_extract_unique(int64_t nao, const int64_t *ptr, const int64_t *idx, int64_t *uptr,
+                                       int64_t *uidx)
+{
+    if (nao < 0 || !ptr || !uptr || (!idx && ptr[nao] > 0)) {
+        fail(QEMB_EINVAL, "bad CSR input");
+        return QEMB_EINVAL;
+    }
+    int64_t n = 0;
+    uptr[0] = 0;
+    for (int64_t mu = 0; mu < nao; ++mu) {
+        for (int64_t k = ptr[mu]; k < ptr[mu + 1]; ++k) {
+            if (idx[k] > mu) break; // sorted lists: the reference stops at the first nu > mu (hpp:155-157)
+            if (uidx) uidx[n] = idx[k];
+            ++n;
+        }
+        uptr[mu + 1] = n;
+    }
+    return n;
+}
+
+namespace {
+// column of the pair (mu,nu): counter over mu, then over the unique list of mu (cpp:248-258).
+// returns -1 when the key was never assigned
+int64_t find_column(const std::vector<int64_t> &uptr, const std::vector<int64_t> &uidx, int64_t mu, int64_t nu)
+{
+    const int64_t hi = std::max(mu, nu), lo = std::min(mu, nu);
+    const int64_t *b = uidx.data() + uptr[hi], *e = uidx.data() + uptr[hi + 1];
+    const int64_t *it = std::lower_bound(b, e, lo);
+    if (it != e && *it == lo) return it - uidx.data();
+    return -1;
+}
+} // namespace
+
+// ------------------------------------------------------------------------------------------------
+// tensor
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_tensor_create(qemb_ctx *ctx, int64_t naux, int64_t nao, const int64_t *exch_ptr,
+                                  const int64_t *exch_idx, qemb_tensor **out)
+{
+    REQ(ctx && out && exch_ptr, "null argument");
+    REQ(naux > 0 && nao > 0, "naux and nao must be positive");
+    REQ(exch_ptr[0] == 0, "exch_ptr[0] must be 0");
+    *out = nullptr;
+    const int64_t nnz = exch_ptr[nao];
+    REQ(nnz >= 0 && nnz < std::numeric_limits<int32_t>::max(), "exch_reachable too large");
+    REQ(nnz == 0 || exch_idx, "null exch_idx");
+    for (int64_t mu = 0; mu < nao; ++mu) {
+        REQ(exch_ptr[mu + 1] >= exch_ptr[mu], "exch_ptr must be non-decreasing");
+        for (int64_t k = exch_ptr[mu]; k < exch_ptr[mu + 1]; ++k) {
+            REQ(exch_idx[k] >= 0 && exch_idx[k] < nao, "exch_reachable entry out of range");
+            REQ(k == exch_ptr[mu] || exch_idx[k] > exch_idx[k - 1], "exch_reachable lists must be sorted ascending");
+        }
+    }
+    DeviceGuard g(ctx->device);
+    qemb_tensor *t = new (std::nothrow) qemb_tensor;
+    if (!t) return fail(QEMB_ENOMEM, "host allocation failed");
+    t->ctx = ctx;
+    t->naux = naux;
+    t->nao = nao;
+    t->ldp = round_up(naux, 128);
+    t->naux16 = round_up(naux, 16);
+    t->rptr.assign(exch_ptr, exch_ptr + nao + 1);
+    t->ridx.assign(exch_idx, exch_idx + nnz);
+    t->uptr.resize(nao + 1);
+    const int64_t nu = qemb_extract_unique(nao, exch_ptr, exch_idx, t->uptr.data(), nullptr);
+    t->uidx.resize(std::max<int64_t>(nu, 1));
+    qemb_extract_unique(nao, exch_ptr, exch_idx, t->uptr.data(), t->uidx.data());
+    t->uidx.resize(nu);
+    t->n_unique = nu;
+    REQ(nu < std::numeric_limits<int32_t>::max(), "too many unique pairs");
+    t->rcol.resize(nnz);
+    std::vector<int32_t> rcol32(nnz), ridx32(nnz);
+    for (int64_t mu = 0; mu < nao; ++mu)
+        for (int64_t k = exch_ptr[mu]; k < exch_ptr[mu + 1]; ++k) {
+            const int64_t c = find_column(t->uptr, t->uidx, mu, exch_idx[k]);
+            t->rcol[k] = c < 0 ? 0 : c; // operator[] default-insert of the reference (cpp:271)
+            rcol32[k] = (int32_t)t->rcol[k];
+            ridx32[k] = (int32_t)exch_idx[k];
+        }
+    int rc = t->data.reserve((size_t)t->ldp * (size_t)std::max<int64_t>(nu, 1) * 8);
+    if (rc == QEMB_OK) rc = t->d_rcol.reserve((size_t)std::max<int64_t>(nnz, 1) * 4);
+    if (rc == QEMB_OK) rc = t->d_ridx.reserve((size_t)std::max<int64_t>(nnz, 1) * 4);
+    if (rc != QEMB_OK) {
+        qemb_tensor_destroy(t);
+        return rc;
+    }
+    cudaStream_t s = ctx->compute;
+    // NaN-fill like cpp:160 so that a column nobody uploaded is detected, pad rows zero
+    CU(launch_fill(t->data.as<double>(), t->ldp * nu, std::numeric_limits<double>::quiet_NaN(), s));
+    CU(launch_zero_rows(t->data.as<double>(), t->ldp, naux, t->ldp, nu, s));
+    ctx->launches += 2;
+    if (nnz) {
+        CU(cudaMemcpyAsync(t->d_rcol.p, rcol32.data(), (size_t)nnz * 4, cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpyAsync(t->d_ridx.p, ridx32.data(), (size_t)nnz * 4, cudaMemcpyHostToDevice, s));
+    }
+    CU(cudaStreamSynchronize(s));
+    *out = t;
+    return QEMB_OK;
+}
+
+extern "C" void qemb_tensor_destroy(qemb_tensor *t)
+{
+    if (!t) return;
+    DeviceGuard g(t->ctx->device);
+    cudaStreamSynchronize(t->ctx->compute);
+    t->data.release();
+    t->d_rcol.release();
+    t->d_ridx.release();
+    delete t;
+}
+
+extern "C" int qemb_tensor_n_unique(const qemb_tensor *t, int64_t *n)
+{
+    REQ(t && n, "null argument");
+    *n = t->n_unique;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_shape(const qemb_tensor *t, int64_t *naux, int64_t *nao, int64_t *n_unique)
+{
+    REQ(t, "null tensor");
+    if (naux) *naux = t->naux;
+    if (nao) *nao = t->nao;
+    if (n_unique) *n_unique = t->n_unique;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_column(const qemb_tensor *t, int64_t mu, int64_t nu, int64_t *col)
+{
+    REQ(t && col, "null argument");
+    if (mu < 0 || nu < 0 || mu >= t->nao || nu >= t->nao) return fail(QEMB_EINDEX, "AO index out of range");
+    const int64_t c = find_column(t->uptr, t->uidx, mu, nu);
+    if (c < 0) return fail(QEMB_EINDEX, "pair (" + std::to_string(mu) + "," + std::to_string(nu) + ") is not in the screened set");
+    *col = c;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_reachable_columns(const qemb_tensor *t, int64_t *col)
+{
+    REQ(t && (col || t->rcol.empty()), "null argument");
+    std::copy(t->rcol.begin(), t->rcol.end(), col);
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_upload(qemb_tensor *t, const double *host, int64_t ld_host, int64_t col0, int64_t ncols)
+{
+    REQ(t && (host || ncols == 0), "null argument");
+    REQ(col0 >= 0 && ncols >= 0 && col0 + ncols <= t->n_unique, "column range outside the tensor");
+    REQ(ld_host >= t->naux, "ld_host < naux");
+    if (ncols == 0) return QEMB_OK;
+    DeviceGuard g(t->ctx->device);
+    cudaStream_t s = t->ctx->compute;
+    CU(cudaMemcpy2DAsync(t->data.as<double>() + col0 * t->ldp, (size_t)t->ldp * 8, host, (size_t)ld_host * 8,
+                         (size_t)t->naux * 8, (size_t)ncols, cudaMemcpyHostToDevice, s));
+    CU(cudaStreamSynchronize(s));
+    t->whitened = false;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_download(const qemb_tensor *t, double *host, int64_t ld_host, int64_t col0, int64_t ncols)
+{
+    REQ(t && (host || ncols == 0), "null argument");
+    REQ(col0 >= 0 && ncols >= 0 && col0 + ncols <= t->n_unique, "column range outside the tensor");
+    REQ(ld_host >= t->naux, "ld_host < naux");
+    if (ncols == 0) return QEMB_OK;
+    DeviceGuard g(t->ctx->device);
+    cudaStream_t s = t->ctx->compute;
+    CU(cudaMemcpy2DAsync(host, (size_t)ld_host * 8, t->data.as<double>() + col0 * t->ldp, (size_t)t->ldp * 8,
+                         (size_t)t->naux * 8, (size_t)ncols, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// metric
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_metric_create(qemb_ctx *ctx, const double *L_host, int64_t ld, int64_t naux, qemb_metric **out)
+{
+    REQ(ctx && L_host && out, "null argument");
+    REQ(naux > 0 && ld >= naux, "bad shape");
+    *out = nullptr;
+    for (int64_t i = 0; i < naux; ++i) {
+        const double d = L_host[i + i * ld];
+        REQ(d == d && d != 0.0, "zero or NaN on the diagonal of L");
+    }
+    DeviceGuard g(ctx->device);
+    qemb_metric *m = new (std::nothrow) qemb_metric;
+    if (!m) return fail(QEMB_ENOMEM, "host allocation failed");
+    m->ctx = ctx;
+    m->naux = naux;
+    m->naux_pad = round_up(naux, TRSM_BLOCK);
+    m->nblocks = (int)(m->naux_pad / TRSM_BLOCK);
+    int rc = m->L.reserve((size_t)m->naux_pad * m->naux_pad * 8);
+    if (rc == QEMB_OK) rc = m->Dinv.reserve((size_t)m->nblocks * TRSM_BLOCK * TRSM_BLOCK * 8);
+    if (rc != QEMB_OK) {
+        qemb_metric_destroy(m);
+        return rc;
+    }
+    cudaStream_t s = ctx->compute;
+    CU(cudaMemsetAsync(m->L.p, 0, (size_t)m->naux_pad * m->naux_pad * 8, s));
+    CU(cudaMemcpy2DAsync(m->L.p, (size_t)m->naux_pad * 8, L_host, (size_t)ld * 8, (size_t)naux * 8, (size_t)naux,
+                         cudaMemcpyHostToDevice, s));
+    CU(launch_set_diag(m->L.as<double>(), m->naux_pad, naux, m->naux_pad, 1.0, s));
+    CU(launch_invert_diag_blocks(m->L.as<double>(), m->naux_pad, m->nblocks, m->Dinv.as<double>(), s));
+    ctx->launches += 2;
+    CU(cudaStreamSynchronize(s));
+    *out = m;
+    return QEMB_OK;
+}
+
+extern "C" void qemb_metric_destroy(qemb_metric *m)
+{
+    if (!m) return;
+    DeviceGuard g(m->ctx->device);
+    cudaStreamSynchronize(m->ctx->compute);
+    m->L.release();
+    m->Dinv.release();
+    delete m;
+}
+
+extern "C" int qemb_tensor_whiten(qemb_tensor *t, const qemb_metric *m)
+{
+    REQ(t && m, "null argument");
+    REQ(t->ctx == m->ctx, "tensor and metric live on different contexts");
+    REQ(t->naux == m->naux, "naux mismatch between tensor and metric");
+    REQ(!t->whitened, "tensor is already whitened");
+    DeviceGuard g(t->ctx->device);
+    TrsmParams p;
+    p.L = m->L.as<double>();
+    p.ldl = m->naux_pad;
+    p.Dinv = m->Dinv.as<double>();
+    p.nblocks = m->nblocks;
+    p.X = t->data.as<double>();
+    p.ldx = t->ldp;
+    p.ncol = t->n_unique;
+    CU(launch_trsm_rows(p, (int)t->naux16, t->ctx->compute));
+    t->ctx->launches += 1;
+    CU(cudaStreamSynchronize(t->ctx->compute));
+    t->whitened = true;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_is_whitened(const qemb_tensor *t, int *flag)
+{
+    REQ(t && flag, "null argument");
+    *flag = t->whitened ? 1 : 0;
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// screen
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_screen_create(qemb_ctx *ctx, const double *S, int64_t ld, int64_t nao, qemb_screen **out)
+{
+    REQ(ctx && S && out, "null argument");
+    REQ(nao > 0 && ld >= nao, "bad shape");
+    *out = nullptr;
+    DeviceGuard g(ctx->device);
+    qemb_screen *sc = new (std::nothrow) qemb_screen;
+    if (!sc) return fail(QEMB_ENOMEM, "host allocation failed");
+    sc->ctx = ctx;
+    sc->nao = nao;
+    int rc = sc->S.reserve((size_t)nao * nao * 8);
+    if (rc != QEMB_OK) {
+        delete sc;
+        return rc;
+    }
+    CU(cudaMemcpy2DAsync(sc->S.p, (size_t)nao * 8, S, (size_t)ld * 8, (size_t)nao * 8, (size_t)nao,
+                         cudaMemcpyHostToDevice, ctx->compute));
+    CU(cudaStreamSynchronize(ctx->compute));
+    *out = sc;
+    return QEMB_OK;
+}
+
+extern "C" void qemb_screen_destroy(qemb_screen *s)
+{
+    if (!s) return;
+    DeviceGuard g(s->ctx->device);
+    s->S.release();
+    delete s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// workspace
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_workspace_create(qemb_ctx *ctx, qemb_workspace **out)
+{
+    REQ(ctx && out, "null argument");
+    *out = nullptr;
+    DeviceGuard g(ctx->device);
+    qemb_workspace *w = new (std::nothrow) qemb_workspace;
+    if (!w) return fail(QEMB_ENOMEM, "host allocation failed");
+    w->ctx = ctx;
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaEventCreateWithFlags(&w->slot[i].uploaded1, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&w->slot[i].uploaded2, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&w->slot[i].consumed, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&w->slot[i].ta_ready, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&w->g_copied[i], cudaEventDisableTiming));
+    }
+    for (int i = 0; i < 5; ++i) CU(cudaEventCreate(&w->ev[i]));
+    for (int i = 0; i < 2; ++i) CU(cudaEventCreate(&w->evs[i]));
+    *out = w;
+    return QEMB_OK;
+}
+
+extern "C" void qemb_workspace_destroy(qemb_workspace *w)
+{
+    if (!w) return;
+    DeviceGuard g(w->ctx->device);
+    qemb_ctx_synchronize(w->ctx);
+    for (int i = 0; i < 2; ++i) {
+        Slot &s = w->slot[i];
+        s.TA.release();
+        s.mask.release();
+        s.plan1.release();
+        s.plan2.release();
+        s.stage1.release();
+        s.stage2.release();
+        s.hmask.release();
+        cudaEventDestroy(s.uploaded1);
+        cudaEventDestroy(s.uploaded2);
+        cudaEventDestroy(s.consumed);
+        cudaEventDestroy(s.ta_ready);
+        cudaEventDestroy(w->g_copied[i]);
+        w->G[i].release();
+    }
+    for (int i = 0; i < 5; ++i) cudaEventDestroy(w->ev[i]);
+    for (int i = 0; i < 2; ++i) cudaEventDestroy(w->evs[i]);
+    w->Bint.release();
+    w->sym.release();
+    for (auto &kv : w->gram_tiles) kv.second.first.release();
+    delete w;
+}
+
+extern "C" int qemb_workspace_bytes(const qemb_workspace *w, int64_t *bytes)
+{
+    REQ(w && bytes, "null argument");
+    size_t b = w->Bint.cap + w->sym.cap + w->G[0].cap + w->G[1].cap;
+    for (int i = 0; i < 2; ++i) b += w->slot[i].TA.cap + w->slot[i].mask.cap + w->slot[i].plan1.cap + w->slot[i].plan2.cap;
+    for (auto &kv : w->gram_tiles) b += kv.second.first.cap;
+    *bytes = (int64_t)b;
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fragment: lists and plans
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+// next slot; waits (host side) until the kernels of the fragment that used it two calls ago are done
+// with its TA / plan tables
+int begin_fragment(qemb_workspace *w, int64_t nao, int64_t nmo)
+{
+    if (w->started) w->cur ^= 1;
+    w->started = true;
+    Slot &s = w->slot[w->cur];
+    if (s.consumed_pending) {
+        CU(cudaEventSynchronize(s.consumed));
+        s.consumed_pending = false;
+    }
+    s.nao = nao;
+    s.nmo = nmo;
+    s.npair = gauss_sum(nmo);
+    s.nA = 0;
+    s.have_plan1 = s.have_plan2 = false;
+    s.plan1_tensor = nullptr;
+    std::fill(s.work, s.work + 8, 0.0);
+    w->have_B = w->have_sym = w->solved = w->have_G = false;
+    return QEMB_OK;
+}
+
+int upload_TA(qemb_workspace *w, const double *TA, int64_t ld)
+{
+    Slot &s = w->slot[w->cur];
+    TRY(s.TA.reserve((size_t)s.nao * s.nmo * 8));
+    CU(cudaMemcpy2DAsync(s.TA.p, (size_t)s.nao * 8, TA, (size_t)ld * 8, (size_t)s.nao * 8, (size_t)s.nmo,
+                         cudaMemcpyHostToDevice, w->ctx->prep));
+    CU(cudaEventRecord(s.ta_ready, w->ctx->prep));
+    return QEMB_OK;
+}
+
+inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+
+// K2a tables: depend only on the lists
+int build_plan2(qemb_workspace *w)
+{
+    Slot &s = w->slot[w->cur];
+    const int64_t nmo = s.nmo, nA = s.nA, npair = s.npair;
+    const int mtiles = (int)((w->mrows + GATHER_TILE_M - 1) / GATHER_TILE_M);
+    int64_t ntiles = 0;
+    for (int64_t a = 0; a < nmo; ++a) ntiles += (int64_t)mtiles * ((nmo - a + GATHER_TILE_N - 1) / GATHER_TILE_N);
+    REQ(ntiles < std::numeric_limits<int32_t>::max(), "too many K2a tiles");
+    size_t o_acol = 0, o_brow = align16(o_acol + nA * 4), o_bcol = align16(o_brow + nA * 4),
+           o_ccol = align16(o_bcol + npair * 4), o_grp = align16(o_ccol + npair * 4),
+           o_tile = align16(o_grp + nmo * sizeof(GatherGroup)), total = align16(o_tile + ntiles * sizeof(int4));
+    TRY(s.stage2.reserve(total));
+    TRY(s.plan2.reserve(total));
+    char *h = static_cast<char *>(s.stage2.p);
+    int *acol = (int *)(h + o_acol), *brow = (int *)(h + o_brow), *bcol = (int *)(h + o_bcol), *ccol = (int *)(h + o_ccol);
+    GatherGroup *grp = (GatherGroup *)(h + o_grp);
+    int4 *tiles = (int4 *)(h + o_tile);
+    for (int64_t k = 0; k < nA; ++k) {
+        acol[k] = (int)k;
+        brow[k] = (int)s.aidx[k];
+    }
+    int64_t bo = 0, nt = 0;
+    double f2 = 0;
+    for (int64_t a = 0; a < nmo; ++a) {
+        const int K = (int)(s.aptr[a + 1] - s.aptr[a]), N = (int)(nmo - a);
+        grp[a] = GatherGroup{K, N, (int)s.aptr[a], (int)bo};
+        for (int64_t n = 0; n < N; ++n) {
+            bcol[bo + n] = (int)(a + n);
+            ccol[bo + n] = (int)(gauss_sum(a + n) + a); // T(max) + min, hpp:75-79
+        }
+        bo += N;
+        const int ntn = (N + GATHER_TILE_N - 1) / GATHER_TILE_N;
+        for (int m = 0; m < mtiles; ++m)
+            for (int n = 0; n < ntn; ++n) tiles[nt++] = make_int4((int)a, m, n, 0);
+        f2 += 2.0 * (double)K * (double)N;
+    }
+    s.work[1] = f2 * (double)w->naux;                               // F_K2a
+    s.work[5] = 8.0 * (double)w->naux * ((double)nA + (double)npair); // Bytes_K2a
+    CU(cudaMemcpyAsync(s.plan2.p, h, total, cudaMemcpyHostToDevice, w->ctx->prep));
+    CU(cudaEventRecord(s.uploaded2, w->ctx->prep));
+    char *d = static_cast<char *>(s.plan2.p);
+    s.pd.acol2 = (const int *)(d + o_acol);
+    s.pd.brow2 = (const int *)(d + o_brow);
+    s.pd.bcol2 = (const int *)(d + o_bcol);
+    s.pd.ccol2 = (const int *)(d + o_ccol);
+    s.pd.groups2 = (const GatherGroup *)(d + o_grp);
+    s.pd.tiles2 = (const int4 *)(d + o_tile);
+    s.pd.ntiles2 = (int)nt;
+    s.have_plan2 = true;
+    return QEMB_OK;
+}
+
+// K1 tables: transpose of the lists (per AO mu: the MOs that reach it) + the tensor's R(mu) lists
+int build_plan1(qemb_workspace *w, const qemb_tensor *t)
+{
+    Slot &s = w->slot[w->cur];
+    const int64_t nao = s.nao, nmo = s.nmo, nA = s.nA;
+    std::vector<int64_t> tptr(nao + 1, 0);
+    for (int64_t k = 0; k < nA; ++k) tptr[s.aidx[k] + 1]++;
+    int64_t ngroups = 0;
+    for (int64_t mu = 0; mu < nao; ++mu) {
+        if (tptr[mu + 1] > 0) ++ngroups;
+        tptr[mu + 1] += tptr[mu];
+    }
+    const int mtiles = (int)((w->mrows + GATHER_TILE_M - 1) / GATHER_TILE_M);
+    int64_t ntiles = 0;
+    for (int64_t mu = 0; mu < nao; ++mu) {
+        const int64_t N = tptr[mu + 1] - tptr[mu];
+        ntiles += (int64_t)mtiles * ((N + GATHER_TILE_N - 1) / GATHER_TILE_N);
+    }
+    REQ(ntiles < std::numeric_limits<int32_t>::max(), "too many K1 tiles");
+    size_t o_bcol = 0, o_ccol = align16(o_bcol + nA * 4), o_grp = align16(o_ccol + nA * 4),
+           o_tile = align16(o_grp + ngroups * sizeof(GatherGroup)), total = align16(o_tile + ntiles * sizeof(int4));
+    TRY(s.stage1.reserve(total));
+    TRY(s.plan1.reserve(total));
+    char *h = static_cast<char *>(s.stage1.p);
+    int *bcol = (int *)(h + o_bcol), *ccol = (int *)(h + o_ccol);
+    GatherGroup *grp = (GatherGroup *)(h + o_grp);
+    int4 *tiles = (int4 *)(h + o_tile);
+    {
+        std::vector<int64_t> fillp(tptr.begin(), tptr.end() - 1);
+        for (int64_t i = 0; i < nmo; ++i)
+            for (int64_t k = s.aptr[i]; k < s.aptr[i + 1]; ++k) {
+                const int64_t q = fillp[s.aidx[k]]++;
+                bcol[q] = (int)i;
+                ccol[q] = (int)k; // offset of (i, mu): running counter over i then mu (cpp:467-482)
+            }
+    }
+    int64_t gi = 0, nt = 0;
+    double f1 = 0;
+    std::vector<uint8_t> col_touched; // U_f of SURVEY 8(d): distinct unique columns read
+    col_touched.assign((size_t)std::max<int64_t>(t->n_unique, 1), 0);
+    int64_t U = 0;
+    for (int64_t mu = 0; mu < nao; ++mu) {
+        const int N = (int)(tptr[mu + 1] - tptr[mu]);
+        if (N == 0) continue;
+        const int K = (int)(t->rptr[mu + 1] - t->rptr[mu]);
+        grp[gi] = GatherGroup{K, N, (int)t->rptr[mu], (int)tptr[mu]};
+        const int ntn = (N + GATHER_TILE_N - 1) / GATHER_TILE_N;
+        for (int m = 0; m < mtiles; ++m)
+            for (int n = 0; n < ntn; ++n) tiles[nt++] = make_int4((int)gi, m, n, 0);
+        ++gi;
+        f1 += 2.0 * (double)K * (double)N;
+        for (int64_t k = t->rptr[mu]; k < t->rptr[mu + 1]; ++k)
+            if (!col_touched[t->rcol[k]]) {
+                col_touched[t->rcol[k]] = 1;
+                ++U;
+            }
+    }
+    s.work[0] = f1 * (double)w->naux;                                                          // F_K1
+    s.work[4] = 8.0 * (double)w->naux * ((double)U + (double)nA) + 8.0 * (double)nao * (double)nmo; // Bytes_K1
+    CU(cudaMemcpyAsync(s.plan1.p, h, total, cudaMemcpyHostToDevice, w->ctx->prep));
+    CU(cudaEventRecord(s.uploaded1, w->ctx->prep));
+    char *d = static_cast<char *>(s.plan1.p);
+    s.pd.bcol1 = (const int *)(d + o_bcol);
+    s.pd.ccol1 = (const int *)(d + o_ccol);
+    s.pd.groups1 = (const GatherGroup *)(d + o_grp);
+    s.pd.tiles1 = (const int4 *)(d + o_tile);
+    s.pd.ntiles1 = (int)nt;
+    s.have_plan1 = true;
+    s.plan1_tensor = t;
+    return QEMB_OK;
+}
+
+int set_lists(qemb_workspace *w, const int64_t *A_ptr, const int64_t *A_idx)
+{
+    Slot &s = w->slot[w->cur];
+    REQ(A_ptr[0] == 0, "A_ptr[0] must be 0");
+    const int64_t nA = A_ptr[s.nmo];
+    REQ(nA >= 0 && nA < std::numeric_limits<int32_t>::max(), "AO_by_MO too large");
+    for (int64_t i = 0; i < s.nmo; ++i) {
+        REQ(A_ptr[i + 1] >= A_ptr[i], "A_ptr must be non-decreasing");
+        for (int64_t k = A_ptr[i]; k < A_ptr[i + 1]; ++k) REQ(A_idx[k] >= 0 && A_idx[k] < s.nao, "AO index out of range");
+    }
+    s.aptr.assign(A_ptr, A_ptr + s.nmo + 1);
+    s.aidx.assign(A_idx, A_idx + nA);
+    s.nA = nA;
+    return QEMB_OK;
+}
+
+int get_gram_tiles(qemb_workspace *w, int nt, const int2 **tiles, int *count)
+{
+    auto it = w->gram_tiles.find(nt);
+    if (it == w->gram_tiles.end()) {
+        std::vector<int2> h((size_t)nt * (nt + 1) / 2);
+        const int64_t n = build_gram_tiles(nt, h.data());
+        DevBuf b;
+        TRY(b.reserve(std::max<size_t>(h.size(), 1) * sizeof(int2)));
+        // blocking copy on the prep stream: happens once per distinct tile count
+        CU(cudaMemcpyAsync(b.p, h.data(), h.size() * sizeof(int2), cudaMemcpyHostToDevice, w->ctx->prep));
+        CU(cudaStreamSynchronize(w->ctx->prep));
+        it = w->gram_tiles.emplace(nt, std::make_pair(b, (int)n)).first;
+    }
+    *tiles = it->second.first.as<int2>();
+    *count = it->second.second;
+    return QEMB_OK;
+}
+
+} // namespace
+
+extern "C" int qemb_fragment_screen(qemb_workspace *w, const qemb_screen *sc, const double *TA, int64_t ld,
+                                    int64_t nao, int64_t nmo, double eps, int64_t *n_mu_i)
+{
+    REQ(w && sc && TA, "null argument");
+    REQ(nao == sc->nao, "TA rows != nao of S_abs");
+    REQ(nmo > 0 && ld >= nao, "bad TA shape");
+    REQ(w->ctx == sc->ctx, "workspace and S_abs live on different contexts");
+    DeviceGuard g(w->ctx->device);
+    TRY(begin_fragment(w, nao, nmo));
+    Slot &s = w->slot[w->cur];
+    TRY(upload_TA(w, TA, ld));
+    TRY(s.mask.reserve((size_t)nao * nmo));
+    TRY(s.hmask.reserve((size_t)nao * nmo));
+    cudaStream_t ps = w->ctx->prep;
+    if (w->ctx->timing) CU(cudaEventRecord(w->evs[0], ps));
+    CU(launch_screen(sc->S.as<double>(), nao, s.TA.as<double>(), nao, (int)nao, (int)nmo, eps, s.mask.as<uint8_t>(), ps));
+    w->ctx->launches += 1;
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->evs[1], ps));
+        w->evs_valid = true;
+    }
+    CU(cudaMemcpyAsync(s.hmask.p, s.mask.p, (size_t)nao * nmo, cudaMemcpyDeviceToHost, ps));
+    CU(cudaStreamSynchronize(ps));
+    const uint8_t *m = static_cast<const uint8_t *>(s.hmask.p);
+    s.aptr.assign(nmo + 1, 0);
+    s.aidx.clear();
+    for (int64_t i = 0; i < nmo; ++i) {
+        const uint8_t *col = m + i * nao;
+        for (int64_t mu = 0; mu < nao; ++mu)
+            if (col[mu]) s.aidx.push_back(mu);
+        s.aptr[i + 1] = (int64_t)s.aidx.size();
+    }
+    s.nA = (int64_t)s.aidx.size();
+    REQ(s.nA < std::numeric_limits<int32_t>::max(), "AO_by_MO too large");
+    if (n_mu_i) *n_mu_i = s.nA;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_set_lists(qemb_workspace *w, const double *TA, int64_t ld, int64_t nao, int64_t nmo,
+                                       const int64_t *A_ptr, const int64_t *A_idx)
+{
+    REQ(w && TA && A_ptr, "null argument");
+    REQ(nao > 0 && nmo > 0 && ld >= nao, "bad TA shape");
+    REQ(A_idx || A_ptr[nmo] == 0, "null A_idx");
+    DeviceGuard g(w->ctx->device);
+    TRY(begin_fragment(w, nao, nmo));
+    TRY(upload_TA(w, TA, ld));
+    TRY(set_lists(w, A_ptr, A_idx));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_get_lists(const qemb_workspace *w, int64_t *A_ptr, int64_t *A_idx)
+{
+    REQ(w && w->started && A_ptr, "no fragment planned");
+    const Slot &s = w->slot[w->cur];
+    std::copy(s.aptr.begin(), s.aptr.end(), A_ptr);
+    if (A_idx) std::copy(s.aidx.begin(), s.aidx.end(), A_idx);
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fragment: kernels
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+int contract_1st(qemb_workspace *w, const qemb_tensor *t, int64_t p0, int64_t p1)
+{
+    Slot &s = w->slot[w->cur];
+    REQ(t->nao == s.nao, "tensor nao != TA rows");
+    REQ(w->ctx == t->ctx, "workspace and tensor live on different contexts");
+    if (p1 < 0) p1 = t->naux;
+    REQ(p0 >= 0 && p0 < p1 && p1 <= t->naux, "bad auxiliary slab");
+    REQ(p0 % 16 == 0 && (p1 % 16 == 0 || p1 == t->naux), "auxiliary slab bounds must be multiples of 16");
+    REQ((p0 == 0 && p1 == t->naux) || t->whitened, "an auxiliary slab needs a whitened tensor");
+    w->ldp = t->ldp;
+    w->naux = p1 - p0;
+    w->mrows = round_up(p1, 16) - p0;
+    TRY(build_plan1(w, t));
+    TRY(w->Bint.reserve((size_t)w->ldp * (size_t)std::max<int64_t>(s.nA, 1) * 8));
+    cudaStream_t cs = w->ctx->compute;
+    CU(cudaStreamWaitEvent(cs, s.ta_ready, 0));
+    CU(cudaStreamWaitEvent(cs, s.uploaded1, 0));
+    GatherParams p;
+    p.Asrc = t->data.as<double>() + p0;
+    p.lda = t->ldp;
+    p.M = (int)w->mrows;
+    p.acol = t->d_rcol.as<int>();
+    p.brow = t->d_ridx.as<int>();
+    p.TA = s.TA.as<double>();
+    p.ldta = s.nao;
+    p.bcol = s.pd.bcol1;
+    p.ccol = s.pd.ccol1;
+    p.C = w->Bint.as<double>();
+    p.ldc = w->ldp;
+    p.groups = s.pd.groups1;
+    p.tiles = s.pd.tiles1;
+    p.ntiles = s.pd.ntiles1;
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->ev[0], cs));
+        w->ev_valid[0] = true;
+    }
+    CU(launch_gather_gemm(p, cs));
+    w->ctx->launches += (p.ntiles > 0);
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->ev[1], cs));
+        w->ev_valid[1] = true;
+    }
+    CU(cudaEventRecord(s.consumed, cs)); // moved forward again by contract_2nd
+    s.consumed_pending = true;
+    w->have_B = true;
+    return QEMB_OK;
+}
+
+int contract_2nd(qemb_workspace *w)
+{
+    Slot &s = w->slot[w->cur];
+    REQ(w->have_B, "contract_1st has not run for this fragment");
+    TRY(build_plan2(w));
+    TRY(w->sym.reserve((size_t)w->ldp * (size_t)s.npair * 8));
+    cudaStream_t cs = w->ctx->compute;
+    CU(cudaStreamWaitEvent(cs, s.uploaded2, 0));
+    GatherParams p;
+    p.Asrc = w->Bint.as<double>();
+    p.lda = w->ldp;
+    p.M = (int)w->mrows;
+    p.acol = s.pd.acol2;
+    p.brow = s.pd.brow2;
+    p.TA = s.TA.as<double>();
+    p.ldta = s.nao;
+    p.bcol = s.pd.bcol2;
+    p.ccol = s.pd.ccol2;
+    p.C = w->sym.as<double>();
+    p.ldc = w->ldp;
+    p.groups = s.pd.groups2;
+    p.tiles = s.pd.tiles2;
+    p.ntiles = s.pd.ntiles2;
+    CU(launch_gather_gemm(p, cs));
+    w->ctx->launches += (p.ntiles > 0);
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->ev[2], cs));
+        w->ev_valid[2] = true;
+    }
+    // TA and the plan tables of this slot are free once K2a has run
+    CU(cudaEventRecord(s.consumed, cs));
+    s.consumed_pending = true;
+    w->have_sym = true;
+    w->solved = false;
+    return QEMB_OK;
+}
+
+int solve(qemb_workspace *w, const qemb_metric *m)
+{
+    Slot &s = w->slot[w->cur];
+    REQ(w->have_sym, "contract_2nd has not run for this fragment");
+    REQ(!w->solved, "already solved");
+    REQ(w->ctx == m->ctx, "workspace and metric live on different contexts");
+    REQ(m->naux == w->naux && m->naux_pad == w->ldp, "naux mismatch between metric and fragment data");
+    TrsmParams p;
+    p.L = m->L.as<double>();
+    p.ldl = m->naux_pad;
+    p.Dinv = m->Dinv.as<double>();
+    p.nblocks = m->nblocks;
+    p.X = w->sym.as<double>();
+    p.ldx = w->ldp;
+    p.ncol = s.npair;
+    cudaStream_t cs = w->ctx->compute;
+    CU(launch_trsm_rows(p, (int)w->mrows, cs));
+    w->ctx->launches += 1;
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->ev[3], cs));
+        w->ev_valid[3] = true;
+    }
+    s.work[2] = (double)m->naux * (double)m->naux * (double)s.npair;                                         // F_K2b
+    s.work[6] = 8.0 * ((double)m->naux * ((double)m->naux + 1) / 2 + 2.0 * (double)m->naux * (double)s.npair); // Bytes_K2b
+    w->solved = true;
+    return QEMB_OK;
+}
+
+// G = X^T X into `dst` (device, ld)
+int gram(qemb_workspace *w, double *dst, int64_t ld)
+{
+    Slot &s = w->slot[w->cur];
+    REQ(w->have_sym, "contract_2nd has not run for this fragment");
+    const int nt = (int)((s.npair + GRAM_TILE - 1) / GRAM_TILE);
+    GramParams p;
+    TRY(get_gram_tiles(w, nt, &p.tiles, &p.ntiles));
+    p.X = w->sym.as<double>();
+    p.ldx = w->ldp;
+    p.ktiles = (int)(w->mrows / 16);
+    p.npair = s.npair;
+    p.G = dst;
+    p.ldg = ld;
+    cudaStream_t cs = w->ctx->compute;
+    if (w->ctx->timing && !w->ev_valid[3]) { // no solve in between: K3 starts where K2a ended
+        CU(cudaEventRecord(w->ev[3], cs));
+        w->ev_valid[3] = true;
+    }
+    CU(launch_gram(p, cs));
+    w->ctx->launches += 1;
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->ev[4], cs));
+        w->ev_valid[4] = true;
+    }
+    s.work[3] = (double)w->naux * (double)s.npair * ((double)s.npair + 1);                 // F_K3 (symmetric count)
+    s.work[7] = 8.0 * ((double)w->naux * (double)s.npair + (double)s.npair * (double)s.npair); // Bytes_K3
+    w->G_last = dst;
+    w->G_last_ld = ld;
+    w->have_G = true;
+    return QEMB_OK;
+}
+
+// G into the workspace's own (double-buffered) storage
+int gram_ws(qemb_workspace *w)
+{
+    Slot &s = w->slot[w->cur];
+    w->gi ^= 1;
+    const int gi = w->gi;
+    TRY(w->G[gi].reserve((size_t)s.npair * (size_t)s.npair * 8));
+    if (w->g_copy_pending[gi]) { // the copy stream may still be reading this buffer
+        CU(cudaStreamWaitEvent(w->ctx->compute, w->g_copied[gi], 0));
+        w->g_copy_pending[gi] = false;
+    }
+    return gram(w, w->G[gi].as<double>(), s.npair);
+}
+
+void reset_events(qemb_workspace *w)
+{
+    for (int i = 0; i < 5; ++i) w->ev_valid[i] = false;
+    w->evs_valid = false;
+}
+
+} // namespace
+
+extern "C" int qemb_fragment_contract_1st(qemb_workspace *w, const qemb_tensor *t)
+{
+    REQ(w && t && w->started, "null argument or no fragment planned");
+    DeviceGuard g(w->ctx->device);
+    return contract_1st(w, t, 0, -1);
+}
+
+extern "C" int qemb_fragment_contract_2nd(qemb_workspace *w)
+{
+    REQ(w && w->started, "null argument or no fragment planned");
+    DeviceGuard g(w->ctx->device);
+    return contract_2nd(w);
+}
+
+extern "C" int qemb_fragment_solve(qemb_workspace *w, const qemb_metric *m)
+{
+    REQ(w && m && w->started, "null argument or no fragment planned");
+    DeviceGuard g(w->ctx->device);
+    return solve(w, m);
+}
+
+extern "C" int qemb_fragment_gram(qemb_workspace *w)
+{
+    REQ(w && w->started, "null argument or no fragment planned");
+    DeviceGuard g(w->ctx->device);
+    return gram_ws(w);
+}
+
+extern "C" int qemb_fragment_get_B(const qemb_workspace *w, double *host, int64_t ld)
+{
+    REQ(w && host && w->have_B, "no K1 result available");
+    const Slot &s = w->slot[w->cur];
+    REQ(ld >= w->naux, "ld < naux");
+    if (s.nA == 0) return QEMB_OK;
+    DeviceGuard g(w->ctx->device);
+    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaMemcpy2D(host, (size_t)ld * 8, w->Bint.p, (size_t)w->ldp * 8, (size_t)w->naux * 8, (size_t)s.nA,
+                    cudaMemcpyDeviceToHost));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_get_sym(const qemb_workspace *w, double *host, int64_t ld)
+{
+    REQ(w && host && w->have_sym, "no K2a result available");
+    const Slot &s = w->slot[w->cur];
+    REQ(ld >= w->naux, "ld < naux");
+    DeviceGuard g(w->ctx->device);
+    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaMemcpy2D(host, (size_t)ld * 8, w->sym.p, (size_t)w->ldp * 8, (size_t)w->naux * 8, (size_t)s.npair,
+                    cudaMemcpyDeviceToHost));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_get_G(const qemb_workspace *w, double *host, int64_t ld)
+{
+    REQ(w && host && w->have_G, "no K3 result available");
+    const Slot &s = w->slot[w->cur];
+    REQ(ld >= s.npair, "ld < npair");
+    DeviceGuard g(w->ctx->device);
+    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaMemcpy2D(host, (size_t)ld * 8, w->G_last, (size_t)w->G_last_ld * 8, (size_t)s.npair * 8, (size_t)s.npair,
+                    cudaMemcpyDeviceToHost));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_G_dev(const qemb_workspace *w, void **dev, int64_t *npair)
+{
+    REQ(w && dev && w->have_G, "no K3 result available");
+    *dev = w->G_last;
+    if (npair) *npair = w->slot[w->cur].npair;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, const qemb_metric *m,
+                                       const qemb_screen *sc, const double *TA, int64_t ld, int64_t nao, int64_t nmo,
+                                       double eps, int64_t p_begin, int64_t p_end, double *out, int64_t ld_out,
+                                       int out_is_device)
+{
+    REQ(w && t && sc && TA && out, "null argument");
+    REQ(t->whitened || m, "a metric is required unless the tensor is whitened");
+    REQ(ld_out >= nmo * (nmo + 1) / 2, "ld_out < npair");
+    DeviceGuard g(w->ctx->device);
+    reset_events(w);
+    TRY(qemb_fragment_screen(w, sc, TA, ld, nao, nmo, eps, nullptr));
+    TRY(contract_1st(w, t, p_begin, p_end));
+    TRY(contract_2nd(w));
+    if (!t->whitened) TRY(solve(w, m));
+    Slot &s = w->slot[w->cur];
+    if (out_is_device) return gram(w, out, ld_out);
+    TRY(gram_ws(w));
+    const int gi = w->gi;
+    // hand G to the copy stream; the compute stream moves on to the next fragment
+    cudaEvent_t done;
+    CU(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    CU(cudaEventRecord(done, w->ctx->compute));
+    CU(cudaStreamWaitEvent(w->ctx->copy, done, 0));
+    CU(cudaEventDestroy(done));
+    CU(cudaMemcpy2DAsync(out, (size_t)ld_out * 8, w->G[gi].p, (size_t)s.npair * 8, (size_t)s.npair * 8, (size_t)s.npair,
+                         cudaMemcpyDeviceToHost, w->ctx->copy));
+    CU(cudaEventRecord(w->g_copied[gi], w->ctx->copy));
+    w->g_copy_pending[gi] = true;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_work(const qemb_workspace *w, const qemb_tensor *, double *out8)
+{
+    REQ(w && out8 && w->started, "no fragment planned");
+    std::copy(w->slot[w->cur].work, w->slot[w->cur].work + 8, out8);
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_times(const qemb_workspace *w, float *ms5)
+{
+    REQ(w && ms5, "null argument");
+    DeviceGuard g(w->ctx->device);
+    CU(cudaStreamSynchronize(w->ctx->prep));
+    CU(cudaStreamSynchronize(w->ctx->compute));
+    for (int i = 0; i < 5; ++i) ms5[i] = 0.f;
+    if (w->evs_valid) CU(cudaEventElapsedTime(&ms5[0], w->evs[0], w->evs[1]));
+    for (int i = 0; i < 4; ++i)
+        if (w->ev_valid[i] && w->ev_valid[i + 1]) CU(cudaEventElapsedTime(&ms5[i + 1], w->ev[i], w->ev[i + 1]));
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// DMMA throughput probe: the gram kernel on an L2-resident problem
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_probe_dmma_tflops(qemb_ctx *ctx, int64_t n, int64_t k, int iters, double *tflops)
+{
+    REQ(ctx && tflops && n > 0 && k > 0 && iters > 0, "bad argument");
+    DeviceGuard g(ctx->device);
+    const int64_t ldx = round_up(k, 128);
+    DevBuf X, G, T;
+    TRY(X.reserve((size_t)ldx * n * 8));
+    TRY(G.reserve((size_t)n * n * 8));
+    const int nt = (int)((n + GRAM_TILE - 1) / GRAM_TILE);
+    std::vector<int2> h((size_t)nt * (nt + 1) / 2);
+    const int64_t ntiles = build_gram_tiles(nt, h.data());
+    TRY(T.reserve(h.size() * sizeof(int2)));
+    cudaStream_t s = ctx->compute;
+    CU(cudaMemcpyAsync(T.p, h.data(), h.size() * sizeof(int2), cudaMemcpyHostToDevice, s));
+    CU(launch_fill(X.as<double>(), ldx * n, 1e-3, s));
+    GramParams p;
+    p.X = X.as<double>();
+    p.ldx = ldx;
+    p.ktiles = (int)(round_up(k, 16) / 16);
+    p.npair = n;
+    p.G = G.as<double>();
+    p.ldg = n;
+    p.tiles = T.as<int2>();
+    p.ntiles = (int)ntiles;
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    CU(launch_gram(p, s));
+    CU(cudaEventRecord(e0, s));
+    for (int i = 0; i < iters; ++i) CU(launch_gram(p, s));
+    CU(cudaEventRecord(e1, s));
+    CU(cudaStreamSynchronize(s));
+    ctx->launches += iters + 2;
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    // executed flops: every tile is a full 128 x 128 x k16 block
+    const double fl = 2.0 * 128.0 * 128.0 * (double)(p.ktiles * 16) * (double)ntiles * iters;
+    *tflops = fl / (ms * 1e-3) / 1e12;
+    X.release();
+    G.release();
+    T.release();
+    return QEMB_OK;
+}

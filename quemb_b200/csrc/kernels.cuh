@@ -1,0 +1,80 @@
+// kernels.cuh -- parameter blocks and host launchers of the sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace qemb {
+
+// ---- K3: G = X^T X (symmetric, lower tiles + mirror) ------------------------------------------
+struct GramParams {
+    const double *X;   // (ldx x npair) column-major, rows = auxiliary index (zero padded to a multiple of 16)
+    int64_t ldx;
+    int ktiles;        // number of 16-row k tiles of the slab
+    int64_t npair;
+    double *G;         // npair x npair, ld = ldg
+    int64_t ldg;
+    const int2 *tiles; // (ti, tj), ti >= tj, L2-friendly order
+    int ntiles;
+};
+cudaError_t launch_gram(const GramParams &p, cudaStream_t s);
+// host: fills the lower-triangular tile list for nt row tiles; returns count
+int64_t build_gram_tiles(int nt, int2 *out /* nt*(nt+1)/2 */);
+constexpr int GRAM_TILE = 128;
+
+// ---- K1 / K2a: grouped gather GEMM --------------------------------------------------------------
+//   C[:, ccol[n]] = sum_k  Asrc[:, acol[k]] * TA[brow[k], bcol[n]]        (k < K, n < N of the group)
+struct GatherGroup {
+    int K, N;
+    int a_off; // offset into acol / brow
+    int b_off; // offset into bcol / ccol
+};
+struct GatherParams {
+    const double *Asrc;
+    int64_t lda;
+    int M; // rows (auxiliary slab), multiple of 2
+    const int *acol;
+    const int *brow;
+    const double *TA;
+    int64_t ldta;
+    const int *bcol;
+    const int *ccol;
+    double *C;
+    int64_t ldc;
+    const GatherGroup *groups;
+    const int4 *tiles; // (group, m tile, n tile, unused)
+    int ntiles;
+};
+cudaError_t launch_gather_gemm(const GatherParams &p, cudaStream_t s);
+constexpr int GATHER_TILE_M = 128;
+constexpr int GATHER_TILE_N = 128;
+
+// ---- K2b: X = L^-1 B, blocked, in place -----------------------------------------------------------
+struct TrsmParams {
+    const double *L;    // naux_pad x naux_pad column-major lower (pad: identity)
+    int64_t ldl;
+    const double *Dinv; // nb blocks of 128x128 column-major: inverse of the diagonal blocks
+    int nblocks;        // = naux_pad / 128
+    double *X;          // ldx x ncol column-major, rows >= nblocks*128 allocated
+    int64_t ldx;
+    int64_t ncol;
+};
+cudaError_t launch_trsm(const TrsmParams &p, cudaStream_t s);
+// same, but rows >= mrows of X are treated as zero on input and left untouched on output
+cudaError_t launch_trsm_rows(const TrsmParams &p, int mrows, cudaStream_t s);
+cudaError_t launch_invert_diag_blocks(const double *L, int64_t ldl, int nblocks, double *Dinv, cudaStream_t s);
+constexpr int TRSM_BLOCK = 128;
+constexpr int TRSM_PANEL = 64;
+
+// ---- screening -------------------------------------------------------------------------------------
+// mask[mu + nao*i] = |sum_nu S[mu,nu] TA[nu,i]| >= eps  (left-to-right, no FMA contraction)
+cudaError_t launch_screen(const double *S, int64_t lds, const double *TA, int64_t ldta, int nao, int nmo,
+                          double eps, uint8_t *mask, cudaStream_t s);
+
+// ---- small utilities --------------------------------------------------------------------------------
+cudaError_t launch_fill(double *p, int64_t n, double v, cudaStream_t s);
+// zero rows [r0, r1) of every column of a column-major matrix
+cudaError_t launch_zero_rows(double *p, int64_t ld, int64_t r0, int64_t r1, int64_t ncol, cudaStream_t s);
+
+cudaError_t launch_set_diag(double *p, int64_t ld, int64_t i0, int64_t i1, double v, cudaStream_t s);
+
+} // namespace qemb

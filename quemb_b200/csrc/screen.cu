@@ -1,0 +1,76 @@
+// screen.cu -- MO->AO screening and small utility kernels.
+//
+// get_AO_per_MO (src/quemb/molbe/_cpp/eri_sparse_DF.cpp:443-465): X = |S_abs * TA|, keep X(mu,i) >= eps.
+// The sparsity pattern has to be bit-exact, so the sum over nu runs strictly left to right with
+// separately rounded multiply and add (__dmul_rn/__dadd_rn forbid FMA contraction): the same value the
+// plain-C oracle (and any non-fast-math scalar loop) produces.  Work is 2*nao^2*nmo flops -- tiny next
+// to the contraction kernels -- so one thread per (mu, i) with coalesced S_abs reads is enough.
+#include "kernels.cuh"
+
+namespace qemb {
+
+__global__ void __launch_bounds__(128) screen_kernel(const double *__restrict__ S, int64_t lds,
+                                                     const double *__restrict__ TA, int64_t ldta, int nao,
+                                                     double eps, uint8_t *__restrict__ mask)
+{
+    const int mu = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (mu >= nao) return;
+    const double *ta = TA + (int64_t)i * ldta;
+    double s = 0.0;
+    for (int nu = 0; nu < nao; ++nu) s = __dadd_rn(s, __dmul_rn(S[mu + (int64_t)nu * lds], ta[nu]));
+    mask[mu + (int64_t)nao * i] = (fabs(s) >= eps) ? 1 : 0;
+}
+
+cudaError_t launch_screen(const double *S, int64_t lds, const double *TA, int64_t ldta, int nao, int nmo,
+                          double eps, uint8_t *mask, cudaStream_t s)
+{
+    if (nao <= 0 || nmo <= 0) return cudaSuccess;
+    dim3 grid((nao + 127) / 128, nmo);
+    screen_kernel<<<grid, 128, 0, s>>>(S, lds, TA, ldta, nao, eps, mask);
+    return cudaGetLastError();
+}
+
+__global__ void fill_kernel(double *p, int64_t n, double v)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        p[i] = v;
+}
+cudaError_t launch_fill(double *p, int64_t n, double v, cudaStream_t s)
+{
+    if (n <= 0) return cudaSuccess;
+    const int64_t blocks = (n + 255) / 256;
+    fill_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, s>>>(p, n, v);
+    return cudaGetLastError();
+}
+
+__global__ void zero_rows_kernel(double *p, int64_t ld, int64_t r0, int64_t nr, int64_t ncol)
+{
+    const int64_t total = nr * ncol;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t c = i / nr, r = i - c * nr;
+        p[c * ld + r0 + r] = 0.0;
+    }
+}
+cudaError_t launch_zero_rows(double *p, int64_t ld, int64_t r0, int64_t r1, int64_t ncol, cudaStream_t s)
+{
+    const int64_t nr = r1 - r0;
+    if (nr <= 0 || ncol <= 0) return cudaSuccess;
+    const int64_t blocks = (nr * ncol + 255) / 256;
+    zero_rows_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, s>>>(p, ld, r0, nr, ncol);
+    return cudaGetLastError();
+}
+
+__global__ void set_diag_kernel(double *p, int64_t ld, int64_t i0, int64_t i1, double v)
+{
+    const int64_t i = i0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < i1) p[i + i * ld] = v;
+}
+cudaError_t launch_set_diag(double *p, int64_t ld, int64_t i0, int64_t i1, double v, cudaStream_t s)
+{
+    if (i1 <= i0) return cudaSuccess;
+    set_diag_kernel<<<(unsigned)((i1 - i0 + 127) / 128), 128, 0, s>>>(p, ld, i0, i1, v);
+    return cudaGetLastError();
+}
+
+} // namespace qemb

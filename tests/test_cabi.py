@@ -1,0 +1,61 @@
+"""CPU: the C-ABI library loads, exports every symbol include/qemb_b200.h declares, its host-side
+index maps are bit-exact, and the compute entry points fail loudly without a GPU (no CPU fallback)."""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import pytest
+
+from quemb_b200 import _lib, indexing
+
+from helpers import CASES, Golden
+
+
+@pytest.fixture(scope="module")
+def L():
+    if not _lib.LIB_PATH.exists():
+        _lib.build()
+    return _lib.lib()
+
+
+def test_exports_every_declared_symbol(L):
+    syms = _lib.declared_symbols()
+    assert len(syms) >= 40
+    missing = [s for s in syms if not hasattr(L, s)]
+    assert not missing
+    assert set(syms) == set(_lib._SIGS), "ctypes table and header disagree"
+
+
+def test_index_maps_host_side(L):
+    for a in range(40):
+        for b in range(40):
+            assert L.qemb_ravel_symmetric(a, b) == indexing.ravel_symmetric(a, b)
+    lo, hi = ctypes.c_int64(), ctypes.c_int64()
+    for i in list(range(3000)) + [2**40 + 12345, 2**52 - 1]:
+        L.qemb_unravel_symmetric(i, ctypes.byref(lo), ctypes.byref(hi))
+        assert (lo.value, hi.value) == indexing.unravel_symmetric(i)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_extract_unique_matches_reference_golden(L, name):
+    g = Golden(name)
+    eptr, eidx = indexing.to_csr(g.exch)
+    uptr = np.zeros(g.nao + 1, dtype=np.int64)
+    n = L.qemb_extract_unique(g.nao, _lib.ptr(eptr), _lib.ptr(eidx), _lib.ptr(uptr), None)
+    uidx = np.zeros(max(n, 1), dtype=np.int64)
+    L.qemb_extract_unique(g.nao, _lib.ptr(eptr), _lib.ptr(eidx), _lib.ptr(uptr), _lib.ptr(uidx))
+    assert indexing.from_csr(uptr, uidx[:n]) == [u.tolist() for u in g.uniq]
+
+
+def test_no_cpu_fallback(L):
+    if _lib.device_count() > 0:
+        pytest.skip("a GPU is visible")
+    h = ctypes.c_void_p()
+    rc = L.qemb_ctx_create(0, ctypes.byref(h))
+    assert rc == _lib.QEMB_ENODEV
+    assert b"no CUDA device" in L.qemb_last_error() or b"cudaGetDeviceCount" in L.qemb_last_error()
+    from quemb_b200 import eri_sparse_DF as q
+
+    with pytest.raises(_lib.QembNoDevice):
+        q.get_AO_per_MO(np.eye(4), np.eye(4), 1e-5)

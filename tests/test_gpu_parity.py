@@ -1,0 +1,224 @@
+"""GPU: parity of the sm_100a path (through the C ABI) with
+  (1) the committed golden fixtures the reference's own compiled extension produced,
+  (2) the plain-C oracle on fresh seeded inputs,
+  (3) size-independent properties at larger sizes.
+Tolerances: index maps / screening pattern bit-exact; (ij|kl) <= 1e-10 max-abs (BASELINE.json north_star)."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from quemb_b200 import _lib, indexing, synthetic as syn
+
+from helpers import CASES, Golden
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-10       # max-abs on (ij|kl)
+TOL_STEP = 1e-12  # K1 / K2a intermediates (pure sums of O(1) products)
+
+
+@pytest.fixture(scope="module")
+def q():
+    from quemb_b200 import eri_sparse_DF as mod
+
+    mod.default_context(0)  # raises QembNoDevice without a B200: no CPU fallback
+    return mod
+
+
+def _tensor(q, g: Golden):
+    return q.SemiSparseSym3DTensor(g.M, (g.naux, g.nao, g.nao), [x.tolist() for x in g.exch])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_index_maps_bit_exact(q, name):
+    g = Golden(name)
+    T = _tensor(q, g)
+    assert T.exch_reachable_unique == [u.tolist() for u in g.uniq]
+    off = T.offsets
+    assert {k: v for k, v in g.offsets.items() if k in off} == off
+    for mu, row in enumerate(T.exch_reachable_with_offsets):
+        for col, nu in row:
+            assert col == g.offsets.get(indexing.ravel_symmetric(mu, nu), 0)
+    assert T.shape == (g.naux, g.nao, g.nao)
+    assert T.nonzero_size == g.naux * g.M.shape[1]
+    np.testing.assert_array_equal(T.unique_dense_data, g.M)
+    mu = g.nao // 2
+    nu = int(g.exch[mu][0]) if len(g.exch[mu]) else mu
+    if len(g.exch[mu]):
+        np.testing.assert_array_equal(T[mu, nu], g.M[:, g.offsets[indexing.ravel_symmetric(mu, nu)]])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_steps_match_reference_golden(q, name):
+    g = Golden(name)
+    T = _tensor(q, g)
+    for f in range(g.n_frag):
+        fr = g.frag(f)
+        A = q.get_AO_per_MO(fr["TA"], g.S_abs, g.eps)
+        assert A == [a.tolist() for a in fr["A"]], "AO_by_MO pattern must be bit-exact"
+        B = q.contract_with_TA_1st(fr["TA"], T, A)
+        assert B.dense_data.shape == fr["B"].shape
+        assert np.abs(B.dense_data - fr["B"]).max() <= TOL_STEP
+        sym = q.contract_with_TA_2nd_to_sym_dense(B, fr["TA"])
+        assert np.abs(sym - fr["sym"]).max() <= TOL_STEP
+        G = q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps)
+        assert G.shape == fr["G"].shape
+        assert np.abs(G - fr["G"]).max() <= TOL
+        assert np.array_equal(G, G.T)
+        # GPU_MatrixHandle route (transform_integral_cuda of the reference)
+        G2 = q.transform_integral_cuda(T, fr["TA"], g.S_abs, q.GPU_MatrixHandle(g.L), g.eps)
+        assert np.array_equal(G, G2)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_whitened_tensor_matches_reference_golden(q, name):
+    """Design option O1: L^-1 applied to (P|mu nu) once instead of per fragment."""
+    g = Golden(name)
+    T = _tensor(q, g)
+    T.whiten(g.L)
+    assert T.whitened
+    for f in range(g.n_frag):
+        fr = g.frag(f)
+        G = q.transform_integral(T, fr["TA"], g.S_abs, None, g.eps)
+        assert np.abs(G - fr["G"]).max() <= TOL
+        assert np.array_equal(G, G.T)
+
+
+def _oracle_G(p, TA):
+    return oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+
+
+@pytest.mark.parametrize(
+    "kw",
+    [
+        dict(n_units=10, ao_per_unit=12, n_end=3, naux=333, frag_halfwidth=1, n_bath=20, sigma=0.7, cond=1e8, seed=101),
+        dict(n_units=6, ao_per_unit=9, n_end=0, naux=129, frag_halfwidth=2, n_bath=9, sigma=0.5, cond=1e10, seed=102),
+        dict(n_units=4, ao_per_unit=3, n_end=1, naux=17, frag_halfwidth=0, n_bath=2, sigma=0.4, cond=1e3, seed=103),
+    ],
+)
+def test_seeded_cases_match_oracle(q, kw):
+    """naux not a multiple of 16/128, several tiles in every dimension, ill-conditioned metric."""
+    p = syn.make_chain_problem(**kw)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    L = q.GPU_MatrixHandle(p.L_PQ)
+    for TA in (p.TAs[0], p.TAs[len(p.TAs) // 2]):
+        A_ref = oracle.get_AO_per_MO(TA, p.S_abs, p.MO_coeff_epsilon)
+        assert q.get_AO_per_MO(TA, p.S_abs, p.MO_coeff_epsilon) == [a.tolist() for a in A_ref]
+        G = q.transform_integral(T, TA, p.S_abs, L, p.MO_coeff_epsilon)
+        Gref = _oracle_G(p, TA)
+        assert np.abs(G - Gref).max() <= TOL
+        assert np.array_equal(G, G.T)
+    Tw = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    Tw.whiten(L)
+    G = q.transform_integral(Tw, p.TAs[0], p.S_abs, None, p.MO_coeff_epsilon)
+    assert np.abs(G - _oracle_G(p, p.TAs[0])).max() <= TOL
+
+
+def test_lattice_case_matches_oracle(q):
+    p = syn.make_lattice_problem(n_side=4, ao_per_site=3, naux=200, n_frag=2, n_bath=12, sigma=0.5, seed=104)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    for TA in p.TAs:
+        G = q.transform_integral(T, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+        assert np.abs(G - _oracle_G(p, TA)).max() <= TOL
+
+
+def test_edge_cases(q):
+    """single MO, MO that reaches no AO (empty list), AO with an empty reachable list."""
+    rng = np.random.default_rng(7)
+    nao, naux = 9, 21
+    S = np.eye(nao)
+    S[0, 1] = S[1, 0] = 0.5
+    exch = [np.nonzero(S[:, mu] >= 1e-10)[0].astype(np.int64) for mu in range(nao)]
+    exch[4] = np.zeros(0, np.int64)  # AO 4 reaches nothing
+    mus, _ = syn.unique_pairs(exch)
+    M = np.asfortranarray(rng.standard_normal((naux, mus.size)))
+    L = np.asfortranarray(np.linalg.cholesky(np.eye(naux) * 2 + 0.1 * np.ones((naux, naux))))
+    T = q.SemiSparseSym3DTensor(M, (naux, nao, nao), exch)
+    # (a) one MO
+    TA = np.zeros((nao, 1), order="F")
+    TA[0, 0] = 1.0
+    G = q.transform_integral(T, TA, S, L, 1e-5)
+    assert G.shape == (1, 1)
+    assert np.abs(G - oracle.transform_integral(M, exch, TA, S, L, 1e-5)).max() <= TOL
+    # (b) second MO is identically zero -> empty A list; third sits on the AO with no partners
+    TA = np.zeros((nao, 3), order="F")
+    TA[1, 0] = 1.0
+    TA[4, 2] = 1.0
+    A = q.get_AO_per_MO(TA, S, 1e-5)
+    assert A == [[0, 1], [], [4]]
+    G = q.transform_integral(T, TA, S, L, 1e-5)
+    Gref = oracle.transform_integral(M, exch, TA, S, L, 1e-5)
+    assert np.abs(G - Gref).max() <= TOL
+    # pair columns that involve the empty MO are exactly zero
+    for hi, lo in [(1, 0), (1, 1), (2, 1)]:
+        assert not G[indexing.ravel_symmetric(hi, lo)].any()
+
+
+def test_error_behaviour(q):
+    nao, naux = 6, 8
+    exch = [list(range(nao))] * nao
+    with pytest.raises(RuntimeError):
+        q.SemiSparseSym3DTensor(np.zeros((naux, 3)), (naux, nao, nao), exch)  # wrong n_unique (cpp:228-238)
+    T = q.SemiSparseSym3DTensor((naux, nao, nao), [[0]] + [[i] for i in range(1, nao)])
+    with pytest.raises(IndexError):
+        T[0, 3]  # unscreened pair (std::out_of_range, cpp:210)
+    # NaN-filled until written (cpp:160)
+    assert np.isnan(T.unique_dense_data).all()
+    view = T.mut_unique_dense_data
+    view[:, :] = 1.5
+    assert (T.unique_dense_data == 1.5).all()
+    with pytest.raises(RuntimeError):
+        q.transform_integral(T, np.zeros((nao + 1, 2)), np.eye(nao), np.eye(naux), 1e-5)  # nao mismatch
+
+
+def test_medium_properties(q):
+    """Larger than the oracle can finish quickly: property checks instead of a reference value.
+    (1) symmetry; (2) K3 against a torch FP64 matmul of the library's own X; (3) aux-slab additivity
+    (the sharded path: sum of partial Gram matrices over P slabs equals the full one)."""
+    import torch
+
+    p = syn.make_chain_problem(n_units=14, ao_per_unit=24, n_end=5, naux=1100, frag_halfwidth=2, n_bath=40,
+                               sigma=0.94, seed=105, n_frag=8)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    T.whiten(p.L_PQ)
+    TA = p.TAs[6]
+    nmo = TA.shape[1]
+    npair = nmo * (nmo + 1) // 2
+    G = q.transform_integral(T, TA, p.S_abs, None, p.MO_coeff_epsilon)
+    assert G.shape == (npair, npair)
+    assert np.array_equal(G, G.T)
+    # X of the same fragment, via the step-wise entry points
+    A = q.get_AO_per_MO(TA, p.S_abs, p.MO_coeff_epsilon)
+    X = q.contract_with_TA_2nd_to_sym_dense(q.contract_with_TA_1st(TA, T, A), TA)
+    Xt = torch.from_numpy(np.ascontiguousarray(X)).cuda()
+    Gt = (Xt.T @ Xt).cpu().numpy()
+    assert np.abs(G - Gt).max() <= TOL
+    # slabs
+    cut = 512
+    G1 = q.transform_integral(T, TA, p.S_abs, None, p.MO_coeff_epsilon, p_range=(0, cut))
+    G2 = q.transform_integral(T, TA, p.S_abs, None, p.MO_coeff_epsilon, p_range=(cut, p.naux))
+    assert np.abs(G1 + G2 - G).max() <= TOL
+
+
+def test_pipelined_calls_with_pinned_outputs(q):
+    """Back-to-back asynchronous transforms (double-buffered slots / G) give the same answers as
+    synchronous ones."""
+    p = syn.make_chain_problem(n_units=8, ao_per_unit=10, n_end=2, naux=160, frag_halfwidth=1, n_bath=10,
+                               sigma=0.6, seed=106)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    L = q.GPU_MatrixHandle(p.L_PQ)
+    ref = [q.transform_integral(T, TA, p.S_abs, L, p.MO_coeff_epsilon).copy() for TA in p.TAs]
+    outs = []
+    for TA in p.TAs:
+        nmo = TA.shape[1]
+        npair = nmo * (nmo + 1) // 2
+        o = _lib.pinned_empty((npair, npair))
+        q.transform_integral(T, TA, p.S_abs, L, p.MO_coeff_epsilon, out=o, synchronize=False)
+        outs.append(o)
+    q.default_context().synchronize()
+    for o, r in zip(outs, ref):
+        assert np.array_equal(o, r)
+    for o in outs:
+        _lib.pinned_free(o)
