@@ -94,6 +94,9 @@ void qemb_metric_destroy(qemb_metric *);
  * device copy; afterwards qemb_fragment_transform skips the per-fragment solve (cpp:615). */
 int qemb_tensor_whiten(qemb_tensor *, const qemb_metric *);
 int qemb_tensor_is_whitened(const qemb_tensor *, int *flag);
+/* device -> device copy of the data (and whitened flag) between two tensors built from the same lists
+ * (keeps a raw copy around when the same molecule is transformed repeatedly) */
+int qemb_tensor_copy_data(qemb_tensor *dst, const qemb_tensor *src);
 
 /* -- screening input ------------------------------------------------------------------------------ */
 int qemb_screen_create(qemb_ctx *, const double *S_abs_host, int64_t ld, int64_t nao, qemb_screen **out);
@@ -142,12 +145,14 @@ int qemb_fragment_G_dev(const qemb_workspace *, void **dev, int64_t *npair);
  *   p_begin/end restrict the auxiliary index to [p_begin, p_end) (aux-sharded fragments; requires a
  *               whitened tensor; pass 0, -1 for the full range).  The result is then the PARTIAL
  *               Gram matrix of that slab, to be summed over ranks.
- * The call is asynchronous on the ctx stream when `out` is pinned or device memory;
- * qemb_ctx_synchronize() completes it. */
+ * The call is asynchronous when `out` is pinned or device memory; qemb_fragment_wait_output(ticket)
+ * or qemb_ctx_synchronize() completes it.  `ticket` may be NULL. */
 int qemb_fragment_transform(qemb_workspace *, const qemb_tensor *, const qemb_metric *,
                             const qemb_screen *, const double *TA_host, int64_t ld, int64_t nao,
                             int64_t nmo, double eps, int64_t p_begin, int64_t p_end, double *out,
-                            int64_t ld_out, int out_is_device);
+                            int64_t ld_out, int out_is_device, int64_t *ticket);
+/* blocks until the host output of the transform that returned `ticket` is complete */
+int qemb_fragment_wait_output(qemb_workspace *, int64_t ticket);
 
 /* Algorithmic work of the last planned fragment (SURVEY 8d formulas): flops and bytes of K1, K2a,
  * K2b, K3 in that order (8 doubles). */
@@ -156,6 +161,10 @@ int qemb_fragment_work(const qemb_workspace *, const qemb_tensor *, double *flop
  * the ctx stream; only recorded when enabled) */
 int qemb_ctx_set_timing(qemb_ctx *, int enabled);
 int qemb_fragment_times(const qemb_workspace *, float *ms5);
+/* CUDA-event marks for whole-step timing: record mark `id` (0..15) on stream 0 = compute, 1 = prep,
+ * 2 = copy; qemb_ctx_mark_elapsed waits for both marks and returns the device time between them. */
+int qemb_ctx_mark(qemb_ctx *, int id, int stream);
+int qemb_ctx_mark_elapsed(qemb_ctx *, int id0, int id1, float *ms);
 /* number of kernel launches issued by this library on this ctx since creation */
 int qemb_ctx_launch_count(const qemb_ctx *, int64_t *n);
 

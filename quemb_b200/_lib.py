@@ -97,11 +97,15 @@ _SIGS = {
     "qemb_fragment_G_dev": (c_int, [c_p, ctypes.POINTER(c_p), ctypes.POINTER(c_i64)]),
     "qemb_fragment_transform": (
         c_int,
-        [c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_dbl, c_i64, c_i64, c_p, c_i64, c_int],
+        [c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_dbl, c_i64, c_i64, c_p, c_i64, c_int, ctypes.POINTER(c_i64)],
     ),
+    "qemb_fragment_wait_output": (c_int, [c_p, c_i64]),
+    "qemb_tensor_copy_data": (c_int, [c_p, c_p]),
     "qemb_fragment_work": (c_int, [c_p, c_p, c_p]),
     "qemb_ctx_set_timing": (c_int, [c_p, c_int]),
     "qemb_fragment_times": (c_int, [c_p, c_p]),
+    "qemb_ctx_mark": (c_int, [c_p, c_int, c_int]),
+    "qemb_ctx_mark_elapsed": (c_int, [c_p, c_int, c_int, ctypes.POINTER(ctypes.c_float)]),
     "qemb_ctx_launch_count": (c_int, [c_p, ctypes.POINTER(c_i64)]),
     "qemb_host_alloc": (c_int, [ctypes.POINTER(c_p), c_i64]),
     "qemb_host_free": (c_int, [c_p]),

@@ -67,6 +67,7 @@ struct qemb_ctx {
     cudaStream_t compute = nullptr, prep = nullptr, copy = nullptr;
     bool timing = false;
     int64_t launches = 0;
+    cudaEvent_t marks[16] = {};
 };
 
 namespace {
@@ -217,6 +218,8 @@ struct qemb_workspace {
     cudaEvent_t g_copied[2] = {nullptr, nullptr};
     bool g_copy_pending[2] = {false, false};
     int gi = 0;
+    int64_t ticket = 0;        // number of host-output transforms issued
+    int ticket_gi[2] = {0, 0};
     double *G_last = nullptr; // where the last K3 wrote
     int64_t G_last_ld = 0;
     bool have_G = false;
@@ -280,6 +283,8 @@ extern "C" void qemb_ctx_destroy(qemb_ctx *c)
     cudaStreamDestroy(c->compute);
     cudaStreamDestroy(c->prep);
     cudaStreamDestroy(c->copy);
+    for (auto &m : c->marks)
+        if (m) cudaEventDestroy(m);
     delete c;
 }
 
@@ -304,6 +309,26 @@ extern "C" int qemb_ctx_set_timing(qemb_ctx *c, int enabled)
 {
     REQ(c != nullptr, "null ctx");
     c->timing = enabled != 0;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_mark(qemb_ctx *c, int id, int stream)
+{
+    REQ(c != nullptr && id >= 0 && id < 16 && stream >= 0 && stream < 3, "bad argument");
+    DeviceGuard g(c->device);
+    if (!c->marks[id]) CU(cudaEventCreate(&c->marks[id]));
+    CU(cudaEventRecord(c->marks[id], stream == 0 ? c->compute : stream == 1 ? c->prep : c->copy));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_mark_elapsed(qemb_ctx *c, int id0, int id1, float *ms)
+{
+    REQ(c != nullptr && ms != nullptr && id0 >= 0 && id0 < 16 && id1 >= 0 && id1 < 16, "bad argument");
+    REQ(c->marks[id0] && c->marks[id1], "mark was never recorded");
+    DeviceGuard g(c->device);
+    CU(cudaEventSynchronize(c->marks[id0]));
+    CU(cudaEventSynchronize(c->marks[id1]));
+    CU(cudaEventElapsedTime(ms, c->marks[id0], c->marks[id1]));
     return QEMB_OK;
 }
 
@@ -595,6 +620,19 @@ extern "C" int qemb_tensor_whiten(qemb_tensor *t, const qemb_metric *m)
     t->ctx->launches += 1;
     CU(cudaStreamSynchronize(t->ctx->compute));
     t->whitened = true;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_copy_data(qemb_tensor *dst, const qemb_tensor *src)
+{
+    REQ(dst && src, "null argument");
+    REQ(dst->ctx == src->ctx, "tensors live on different contexts");
+    REQ(dst->naux == src->naux && dst->nao == src->nao && dst->n_unique == src->n_unique && dst->rcol == src->rcol,
+        "tensors have different shapes or lists");
+    DeviceGuard g(dst->ctx->device);
+    CU(cudaMemcpyAsync(dst->data.p, src->data.p, (size_t)src->ldp * (size_t)src->n_unique * 8, cudaMemcpyDeviceToDevice,
+                       dst->ctx->compute));
+    dst->whitened = src->whitened;
     return QEMB_OK;
 }
 
@@ -1210,8 +1248,9 @@ extern "C" int qemb_fragment_G_dev(const qemb_workspace *w, void **dev, int64_t 
 extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, const qemb_metric *m,
                                        const qemb_screen *sc, const double *TA, int64_t ld, int64_t nao, int64_t nmo,
                                        double eps, int64_t p_begin, int64_t p_end, double *out, int64_t ld_out,
-                                       int out_is_device)
+                                       int out_is_device, int64_t *ticket)
 {
+    if (ticket) *ticket = -1;
     REQ(w && t && sc && TA && out, "null argument");
     REQ(t->whitened || m, "a metric is required unless the tensor is whitened");
     REQ(ld_out >= nmo * (nmo + 1) / 2, "ld_out < npair");
@@ -1235,6 +1274,20 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
                          cudaMemcpyDeviceToHost, w->ctx->copy));
     CU(cudaEventRecord(w->g_copied[gi], w->ctx->copy));
     w->g_copy_pending[gi] = true;
+    w->ticket += 1; // ticket k uses G buffer / event k & 1 (gi toggles once per host-output transform)
+    w->ticket_gi[w->ticket & 1] = gi;
+    if (ticket) *ticket = w->ticket;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_wait_output(qemb_workspace *w, int64_t ticket)
+{
+    REQ(w, "null workspace");
+    REQ(ticket >= 1 && ticket <= w->ticket, "unknown ticket");
+    // the event of this parity was last recorded by this ticket or by a later one of the same parity on the
+    // same in-order copy stream, so waiting for it is always sufficient
+    DeviceGuard g(w->ctx->device);
+    CU(cudaEventSynchronize(w->g_copied[w->ticket_gi[ticket & 1]]));
     return QEMB_OK;
 }
 

@@ -79,6 +79,14 @@ class Context:
     def set_timing(self, enabled: bool) -> None:
         check(lib().qemb_ctx_set_timing(self._h, c_int(1 if enabled else 0)))
 
+    def mark(self, id: int, stream: str = "compute") -> None:
+        check(lib().qemb_ctx_mark(self._h, c_int(id), c_int({"compute": 0, "prep": 1, "copy": 2}[stream])))
+
+    def mark_elapsed_ms(self, id0: int, id1: int) -> float:
+        ms = ctypes.c_float()
+        check(lib().qemb_ctx_mark_elapsed(self._h, c_int(id0), c_int(id1), ctypes.byref(ms)))
+        return float(ms.value)
+
     @property
     def launch_count(self) -> int:
         n = c_i64()
@@ -115,7 +123,11 @@ class Workspace:
         h = c_p()
         check(lib().qemb_workspace_create(self.ctx._h, ctypes.byref(h)))
         self._h = h
+        self.last_ticket = -1
         self._finalizer = weakref.finalize(self, lib().qemb_workspace_destroy, h)
+
+    def wait_output(self, ticket: int) -> None:
+        check(lib().qemb_fragment_wait_output(self._h, c_i64(ticket)))
 
     @property
     def device_bytes(self) -> int:
@@ -326,6 +338,11 @@ class SemiSparseSym3DTensor:
         m = _metric_for(L_PQ, self.ctx)
         check(lib().qemb_tensor_whiten(self._h, m._h))
 
+    def copy_data_from(self, other: "SemiSparseSym3DTensor") -> None:
+        """Device-to-device copy of the data of a tensor built from the same lists."""
+        other._flush()
+        check(lib().qemb_tensor_copy_data(self._h, other._h))
+
     @property
     def whitened(self) -> bool:
         f = c_int()
@@ -532,12 +549,41 @@ def transform_integral(
     ld_out = npair
     if not (out.flags.f_contiguous or out.flags.c_contiguous):
         raise _lib.QembError("out must be contiguous")  # G is symmetric: C and F order coincide
+    ticket = c_i64()
     check(lib().qemb_fragment_transform(
         ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
-        c_i64(nmo), c_dbl(MO_coeff_epsilon), c_i64(p_range[0]), c_i64(p_range[1]), ptr(out), c_i64(ld_out), c_int(0)))
+        c_i64(nmo), c_dbl(MO_coeff_epsilon), c_i64(p_range[0]), c_i64(p_range[1]), ptr(out), c_i64(ld_out), c_int(0),
+        ctypes.byref(ticket)))
+    ws.last_ticket = ticket.value
     if synchronize:
         ctx.synchronize()
     return out
+
+
+def transform_integral_device(
+    int_P_mu_nu: SemiSparseSym3DTensor,
+    TA,
+    S_abs,
+    L_PQ,
+    MO_coeff_epsilon: float,
+    out_dev_ptr: int,
+    ld_out: int,
+    *,
+    ws: Workspace | None = None,
+    p_range: tuple[int, int] = (0, -1),
+) -> None:
+    """Same path, but (ij|kl) is written straight into caller-owned device memory (e.g. a torch
+    tensor's ``data_ptr()``) and nothing travels to the host.  Asynchronous."""
+    ctx = int_P_mu_nu.ctx
+    ws = ws or default_workspace(ctx)
+    TA = _f64(TA, "TA")
+    int_P_mu_nu._flush()
+    sc = _screen_for(S_abs, ctx)
+    m = None if (L_PQ is None) else _metric_for(L_PQ, ctx)
+    check(lib().qemb_fragment_transform(
+        ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
+        c_i64(TA.shape[1]), c_dbl(MO_coeff_epsilon), c_i64(p_range[0]), c_i64(p_range[1]), c_p(out_dev_ptr),
+        c_i64(ld_out), c_int(1), None))
 
 
 def transform_integral_cuda(int_P_mu_nu, TA, S_abs, L_PQ: GPU_MatrixHandle, MO_coeff_epsilon: float) -> np.ndarray:

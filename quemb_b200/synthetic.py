@@ -141,6 +141,7 @@ def make_P_mu_nu(
     L_PQ: np.ndarray,
     rng,
     whitened_scale: bool = True,
+    matmul=None,
 ) -> np.ndarray:
     """unique_dense_data (naux, n_unique) = L @ Y, Y ~ N(0,1) exp(-d^2/4 sigma^2)/sqrt(naux)."""
     naux = L_PQ.shape[0]
@@ -150,7 +151,7 @@ def make_P_mu_nu(
     Y = rng.standard_normal((naux, mus.size)) * decay[None, :]
     if whitened_scale:
         Y /= np.sqrt(naux)
-        M = np.tril(L_PQ) @ Y
+        M = (matmul or np.matmul)(np.tril(L_PQ), Y)  # `matmul`: optional accelerator for the big cases
     else:
         M = Y
     return np.asfortranarray(M)
@@ -171,6 +172,7 @@ def make_chain_problem(
     MO_coeff_epsilon: float = 1e-5,
     AO_coeff_epsilon: float = 1e-10,
     name: str = "chain",
+    matmul=None,
 ) -> Problem:
     """Alkane-like chain. One fragment per unit (centre unit +- halfwidth units,
     clipped at the ends — edge fragments are smaller, like BE-n on a chain)."""
@@ -180,7 +182,7 @@ def make_chain_problem(
     S_abs = gaussian_S_abs(r, sigma)
     exch = get_AO_per_AO(S_abs, AO_coeff_epsilon)
     L = metric_cholesky(naux, cond, rng)
-    M = make_P_mu_nu(r, sigma, exch, L, rng)
+    M = make_P_mu_nu(r, sigma, exch, L, rng, matmul=matmul)
     unit_of_ao = np.concatenate(
         [
             np.zeros(n_end, np.int64),
@@ -257,17 +259,17 @@ def make_lattice_problem(
 
 # Named shapes from BASELINE.json / SURVEY.md §8(d) -------------------------
 
-def octane_like(seed: int = SEED, n_frag: int | None = None) -> Problem:
+def octane_like(seed: int = SEED, n_frag: int | None = None, matmul=None) -> Problem:
     """nao 202, naux 700, 8 fragments (C8H18 cc-pVDZ / cc-pVDZ-RI, BE3-like)."""
     return make_chain_problem(
         n_units=8, ao_per_unit=24, n_end=5, naux=700, frag_halfwidth=2,
-        n_bath=33, seed=seed, n_frag=n_frag, name="octane-like",
+        n_bath=33, seed=seed, n_frag=n_frag, name="octane-like", matmul=matmul,
     )
 
 
-def c32h66_like(seed: int = SEED, n_frag: int | None = None) -> Problem:
+def c32h66_like(seed: int = SEED, n_frag: int | None = None, matmul=None) -> Problem:
     """nao 778, naux 2716, 32 fragments, nmo <= 220 (C32H66 cc-pVDZ/-RI BE3-like)."""
     return make_chain_problem(
         n_units=32, ao_per_unit=24, n_end=5, naux=2716, frag_halfwidth=2,
-        n_bath=100, seed=seed, n_frag=n_frag, name="C32H66-like",
+        n_bath=100, seed=seed, n_frag=n_frag, name="C32H66-like", matmul=matmul,
     )

@@ -40,7 +40,7 @@ for f, TA in enumerate(p.TAs[1:1 + nfrag] if which == "c32" else p.TAs[:nfrag]):
     for rep in range(2):
         t = time.time()
         _lib.check(_lib.lib().qemb_fragment_transform(ws._h, T._h, None if whiten else L._h, q._screen_for(p.S_abs, ctx)._h,
-            _lib.ptr(TA), TA.shape[0], TA.shape[0], nmo, 1e-5, 0, -1, _lib.c_p(out.data_ptr()), npair, 1))
+            _lib.ptr(TA), TA.shape[0], TA.shape[0], nmo, 1e-5, 0, -1, _lib.c_p(out.data_ptr()), npair, 1, None))
         ctx.synchronize(); wall = time.time() - t
     ms = ws.times_ms(); wk = ws.work()
     print(f"frag {f} nmo {nmo} npair {npair} wall {wall*1e3:.1f} ms  times {ms}")
