@@ -160,6 +160,16 @@ int qemb_fragment_work(const qemb_workspace *, const qemb_tensor *, double *flop
 /* device time in ms of the kernels of the last fragment: screen, K1, K2a, K2b, K3 (CUDA events on
  * the ctx stream; only recorded when enabled) */
 int qemb_ctx_set_timing(qemb_ctx *, int enabled);
+/* How a host-bound (ij|kl) matrix travels.  1 (default): only the lower triangle crosses PCIe, in column
+ * groups, and the library's host threads rebuild the upper triangle while later groups and the next
+ * fragment are in flight (the reference's GPU variant copies the full syrk result and mirrors it on one
+ * host thread, cpp:684-708).  0: the full square crosses PCIe. */
+int qemb_ctx_set_output_mode(qemb_ctx *, int mode);
+/* number of host worker threads of the library (QEMB_HOST_THREADS, default: cores in the affinity mask - 1) */
+int qemb_host_threads(int *n);
+/* G[c + ld*r] = G[r + ld*c] for all r > c of an n x n host matrix (the host half of output mode 1; also the
+ * replacement of the reference's serial mirror loop, cpp:700-708). */
+int qemb_host_mirror_lower(double *G, int64_t ld, int64_t n);
 int qemb_fragment_times(const qemb_workspace *, float *ms5);
 /* CUDA-event marks for whole-step timing: record mark `id` (0..15) on stream 0 = compute, 1 = prep,
  * 2 = copy; qemb_ctx_mark_elapsed waits for both marks and returns the device time between them. */

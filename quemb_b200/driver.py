@@ -49,7 +49,7 @@ def partition_lpt(costs: Sequence[float], n_parts: int) -> list[list[int]]:
 class FragmentERIBuilder:
     """Device-resident state of one molecule on ONE GPU + the pipelined per-fragment loop."""
 
-    def __init__(self, device: int = 0, max_nmo: int | None = None, n_host_buffers: int = 2):
+    def __init__(self, device: int = 0, max_nmo: int | None = None, n_host_buffers: int = 3):
         self.ctx = q.default_context(device)
         self.ws = q.Workspace(self.ctx)
         self.tensor: q.SemiSparseSym3DTensor | None = None

@@ -76,6 +76,11 @@ class Context:
     def synchronize(self) -> None:
         check(lib().qemb_ctx_synchronize(self._h))
 
+    def set_output_mode(self, triangle: bool) -> None:
+        """True (default): host-bound G crosses PCIe as its lower triangle and is mirrored by host threads;
+        False: the full square crosses PCIe."""
+        check(lib().qemb_ctx_set_output_mode(self._h, c_int(1 if triangle else 0)))
+
     def set_timing(self, enabled: bool) -> None:
         check(lib().qemb_ctx_set_timing(self._h, c_int(1 if enabled else 0)))
 

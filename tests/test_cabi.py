@@ -59,3 +59,22 @@ def test_no_cpu_fallback(L):
 
     with pytest.raises(_lib.QembNoDevice):
         q.get_AO_per_MO(np.eye(4), np.eye(4), 1e-5)
+
+
+@pytest.mark.parametrize("n", [1, 7, 255, 1030, 2051])
+def test_host_mirror_lower(n):
+    """Host half of output mode 1 (no GPU needed): upper triangle rebuilt from the lower one, bit-exact."""
+    import ctypes
+
+    L = _lib.lib()
+    rng = np.random.default_rng(n)
+    A = rng.standard_normal((n, n))
+    S = np.tril(A) + np.tril(A, -1).T
+    ld = n + 3
+    buf = np.full((n, ld), np.nan)          # column c of the column-major matrix = buf[c, :n]
+    buf[:, :n] = np.where(np.arange(n)[None, :] >= np.arange(n)[:, None], S, np.nan)  # rows r >= c only
+    _lib.check(L.qemb_host_mirror_lower(_lib.ptr(buf), ctypes.c_int64(ld), ctypes.c_int64(n)))
+    np.testing.assert_array_equal(buf[:, :n], S)
+    nt = ctypes.c_int()
+    _lib.check(L.qemb_host_threads(ctypes.byref(nt)))
+    assert nt.value >= 1
