@@ -177,6 +177,9 @@ int qemb_ctx_mark(qemb_ctx *, int id, int stream);
 int qemb_ctx_mark_elapsed(qemb_ctx *, int id0, int id1, float *ms);
 /* number of kernel launches issued by this library on this ctx since creation */
 int qemb_ctx_launch_count(const qemb_ctx *, int64_t *n);
+/* bytes this context has handed to the copy engines so far: host->device (tensor, metric, S_abs, TA, plan
+ * tables) and device->host ((ij|kl) transfers; the screening mask travels through mapped memory) */
+int qemb_ctx_transfer_bytes(const qemb_ctx *, int64_t *h2d, int64_t *d2h);
 
 /* pinned host memory helpers (so that Python callers can hand out asynchronous buffers) */
 int qemb_host_alloc(void **p, int64_t bytes);

@@ -110,6 +110,7 @@ _SIGS = {
     "qemb_ctx_mark": (c_int, [c_p, c_int, c_int]),
     "qemb_ctx_mark_elapsed": (c_int, [c_p, c_int, c_int, ctypes.POINTER(ctypes.c_float)]),
     "qemb_ctx_launch_count": (c_int, [c_p, ctypes.POINTER(c_i64)]),
+    "qemb_ctx_transfer_bytes": (c_int, [c_p, ctypes.POINTER(c_i64), ctypes.POINTER(c_i64)]),
     "qemb_host_alloc": (c_int, [ctypes.POINTER(c_p), c_i64]),
     "qemb_host_free": (c_int, [c_p]),
     "qemb_probe_dmma_tflops": (c_int, [c_p, c_i64, c_i64, c_int, ctypes.POINTER(c_dbl)]),

@@ -74,6 +74,8 @@ struct qemb_ctx {
     // how a host-bound G travels: 1 = lower triangle over PCIe + mirror on the host cores (default),
     // 0 = the full square over PCIe
     int out_mode = 1;
+    int num_sms = 148;
+    int64_t h2d_bytes = 0, d2h_bytes = 0; // bytes handed to the copy engines (uploads / G transfers)
     // pinned bounce buffers for uploads out of pageable host memory
     void *bounce[2] = {nullptr, nullptr};
     cudaEvent_t bounce_free[2] = {nullptr, nullptr};
@@ -172,6 +174,7 @@ int upload_2d(qemb_ctx *c, void *dst, size_t dpitch, const void *src, size_t spi
               cudaStream_t s)
 {
     if (width == 0 || height == 0) return QEMB_OK;
+    c->h2d_bytes += (int64_t)(width * height);
     cudaPointerAttributes at;
     cudaError_t e = cudaPointerGetAttributes(&at, src);
     if (e != cudaSuccess) (void)cudaGetLastError();
@@ -337,6 +340,7 @@ extern "C" int qemb_ctx_create(int device, qemb_ctx **out)
     qemb_ctx *c = new (std::nothrow) qemb_ctx;
     if (!c) return fail(QEMB_ENOMEM, "host allocation failed");
     c->device = device;
+    c->num_sms = prop.multiProcessorCount;
     CU(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->prep, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
@@ -451,6 +455,14 @@ extern "C" int qemb_ctx_launch_count(const qemb_ctx *c, int64_t *n)
 {
     REQ(c != nullptr && n != nullptr, "null argument");
     *n = c->launches;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_transfer_bytes(const qemb_ctx *c, int64_t *h2d, int64_t *d2h)
+{
+    REQ(c != nullptr && h2d != nullptr && d2h != nullptr, "null argument");
+    *h2d = c->h2d_bytes;
+    *d2h = c->d2h_bytes;
     return QEMB_OK;
 }
 
@@ -889,6 +901,7 @@ int upload_TA(qemb_workspace *w, const double *TA, int64_t ld)
     TRY(s.TA.reserve((size_t)s.nao * s.nmo * 8));
     CU(cudaMemcpy2DAsync(s.TA.p, (size_t)s.nao * 8, TA, (size_t)ld * 8, (size_t)s.nao * 8, (size_t)s.nmo,
                          cudaMemcpyHostToDevice, w->ctx->prep));
+    w->ctx->h2d_bytes += s.nao * s.nmo * 8;
     CU(cudaEventRecord(s.ta_ready, w->ctx->prep));
     return QEMB_OK;
 }
@@ -934,6 +947,7 @@ int build_plan2(qemb_workspace *w)
     }
     s.work[1] = f2 * (double)w->naux;                               // F_K2a
     s.work[5] = 8.0 * (double)w->naux * ((double)nA + (double)npair); // Bytes_K2a
+    w->ctx->h2d_bytes += (int64_t)total;
     CU(cudaMemcpyAsync(s.plan2.p, h, total, cudaMemcpyHostToDevice, w->ctx->prep));
     CU(cudaEventRecord(s.uploaded2, w->ctx->prep));
     char *d = static_cast<char *>(s.plan2.p);
@@ -1007,6 +1021,7 @@ int build_plan1(qemb_workspace *w, const qemb_tensor *t)
     }
     s.work[0] = f1 * (double)w->naux;                                                          // F_K1
     s.work[4] = 8.0 * (double)w->naux * ((double)U + (double)nA) + 8.0 * (double)nao * (double)nmo; // Bytes_K1
+    w->ctx->h2d_bytes += (int64_t)total;
     CU(cudaMemcpyAsync(s.plan1.p, h, total, cudaMemcpyHostToDevice, w->ctx->prep));
     CU(cudaEventRecord(s.uploaded1, w->ctx->prep));
     char *d = static_cast<char *>(s.plan1.p);
@@ -1254,7 +1269,7 @@ int gram(qemb_workspace *w, double *dst, int64_t ld)
         CU(cudaEventRecord(w->ev[3], cs));
         w->ev_valid[3] = true;
     }
-    CU(launch_gram(p, cs));
+    CU(launch_gram(p, w->ctx->num_sms, cs));
     w->ctx->launches += 1;
     if (w->ctx->timing) {
         CU(cudaEventRecord(w->ev[4], cs));
@@ -1407,6 +1422,7 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
 {
     cudaStream_t cs = w->ctx->copy;
     if (w->ctx->out_mode == 0 || n < 1024) {
+        w->ctx->d2h_bytes += n * n * 8;
         CU(cudaMemcpy2DAsync(out, (size_t)ld_out * 8, G, (size_t)n * 8, (size_t)n * 8, (size_t)n, cudaMemcpyDeviceToHost, cs));
         return QEMB_OK;
     }
@@ -1423,6 +1439,7 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         int64_t width = std::max<int64_t>(256, (target / (8 * rows) + 255) / 256 * 256);
         int64_t c1 = std::min(n, c0 + width);
         if (n - c1 < 256) c1 = n;
+        w->ctx->d2h_bytes += rows * 8 * (c1 - c0);
         CU(cudaMemcpy2DAsync(out + c0 + ld_out * c0, (size_t)ld_out * 8, G + c0 + n * c0, (size_t)n * 8, (size_t)rows * 8,
                              (size_t)(c1 - c0), cudaMemcpyDeviceToHost, cs));
         MirrorCb *cb = new MirrorCb{&job, out, ld_out, n, c0, c1, c1 == n};
@@ -1540,9 +1557,9 @@ extern "C" int qemb_probe_dmma_tflops(qemb_ctx *ctx, int64_t n, int64_t k, int i
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0));
     CU(cudaEventCreate(&e1));
-    CU(launch_gram(p, s));
+    CU(launch_gram(p, ctx->num_sms, s));
     CU(cudaEventRecord(e0, s));
-    for (int i = 0; i < iters; ++i) CU(launch_gram(p, s));
+    for (int i = 0; i < iters; ++i) CU(launch_gram(p, ctx->num_sms, s));
     CU(cudaEventRecord(e1, s));
     CU(cudaStreamSynchronize(s));
     ctx->launches += iters + 2;

@@ -2,85 +2,174 @@
 // src/quemb/molbe/_cpp/eri_sparse_DF.cpp:620, and the cuBLAS Dsyrk + host mirror of its GPU variant,
 // cpp:684-708).
 //
-// Design: symmetric FP64 tensor-core contraction.  X is (ldx x npair) column-major, i.e. every pair
-// column is k-contiguous -- exactly the "row.col" operand order of DMMA for both operands, so the
-// tile loads are plain 128-byte row segments.  Only the nt(nt+1)/2 lower tiles are computed
-// (naux*npair*(npair+1) flops instead of the reference CPU path's full 2*naux*npair^2 GEMM); every
-// off-diagonal tile is also stored transposed, so the full npair x npair square the consumers read
-// (pfrag.py:383, mbe.py:1155) is emitted directly in s4 pair order with no host mirror pass.
+// Symmetric FP64 tensor-core contraction.  X is (ldx x npair) column-major, i.e. every pair column is
+// k-contiguous -- exactly the "row.col" operand order of DMMA for both operands.  Only the nt(nt+1)/2
+// lower 128x128 tiles are computed (naux*npair*(npair+1) flops instead of the reference CPU path's full
+// 2*naux*npair^2 GEMM); every off-diagonal tile is also stored transposed, so the full npair x npair
+// square the consumers read (pfrag.py:383, mbe.py:1155) is emitted directly in s4 pair order.
 //
-// CTA tile 128x128x16, 8 warps (2 x 4), warp tile 64x32 = 32 DMMA.8x8x4 accumulators (128 regs),
-// STAGES-deep cp.async ring (40 KB per stage).  Tiles are ordered in bands of GROUP row-tiles so that
-// the 148 concurrently resident tiles share ~2*sqrt(148) X panels in the 126 MB L2.
+// Data movement (measured on B200, npair 24310, naux 2716: 35.9 TFLOP/s = 96 % of the 37.2 TFLOP/s DMMA
+// peak, cuBLAS DGEMM 35.5; the cp.async + bar.sync version of the same tiling reached 29-31):
+//   * one producer warp issues TMA tile loads (cp.async.bulk.tensor.2d, 128B swizzle) of the two
+//     128-row x 16-k operand slabs of X into a ring of shared-memory stages;
+//   * eight consumer warps (64x32 register tiles of DMMA.8x8x4 accumulators) wait on the stage's "full"
+//     mbarrier, read their fragments with 64-bit LDS, and release the stage through its "empty"
+//     mbarrier -- there is NO CTA-wide barrier in the main loop, so a warp that waits for shared memory
+//     never holds back the other warp of its scheduler (the cp.async version idles the DMMA pipe ~16 %
+//     of the time on bar.sync + LDS + cp.async-wait stalls that hit all warps at once; ncu, profiles/);
+//   * the kernel is persistent (one CTA per SM): the producer runs ahead into the next tile while the
+//     consumers store the finished one, which hides the pipeline fill and the epilogue.
+//
+// Bank conflicts: with the 128B swizzle the 16-byte chunk c of row r sits at chunk c ^ (r & 7).  The DMMA
+// fragment pattern (lane = 4g + t reads row g, k = t) would then be 2-way conflicted, so the k index
+// inside a 16-wide stage is permuted: k-step ks, lane t reads k = 8*(t>>1) + 2*ks + (t&1).  Both
+// operands use the same permutation, so the sum over k is unchanged; the 16 lanes of an LDS.64 phase hit
+// 16 distinct bank pairs.
+#include <cuda.h>
+
 #include "dmma_core.cuh"
 #include "kernels.cuh"
 
 namespace qemb {
 
 namespace {
-constexpr int TM = GRAM_TILE, TN = GRAM_TILE;
-constexpr int STAGES = 4;
-constexpr int STAGE_DOUBLES = (TM + TN) * PITCH_K;
-constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8;
-constexpr int NTHREADS = 256;
+constexpr int TM = 128, TN = 128;
 constexpr int WM = 64, WN = 32;
+constexpr int NCONSUMER_WARPS = 8;
+constexpr int NTHREADS = 32 * (NCONSUMER_WARPS + 4); // + one producer warpgroup (register file is split per
+                                                     // scheduler: a 9th warp would cap everybody at 168 regs)
+constexpr int STAGES = 6;
+constexpr int TILE_BYTES = 128 * BK * 8; // 16 KB per operand slab
+constexpr int STAGE_BYTES = 2 * TILE_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /* alignment slack */ + 2 * STAGES * 8;
 
-__device__ __forceinline__ void load_rows_kmajor(double *dst, const double *__restrict__ X, int64_t ldx,
-                                                 int64_t row0, int64_t nrows_total, int k0, int tid)
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
 {
-    // 128 rows x 16 k = 128 x 8 chunks of 16 B; 8 consecutive threads fetch one 128-byte row segment
-#pragma unroll
-    for (int r = 0; r < (TM * 8) / NTHREADS; ++r) {
-        const int idx = tid + NTHREADS * r;
-        const int row = idx >> 3, ch = idx & 7;
-        const int64_t grow = row0 + row;
-        const bool ok = grow < nrows_total;
-        const double *src = X + (ok ? grow : 0) * ldx + k0 + ch * 2;
-        cp_async16(dst + row * PITCH_K + ch * 2, src, ok);
-    }
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, int bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, int parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(smem_u32(dst)),
+        "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+        : "memory");
 }
 } // namespace
 
-__global__ void __launch_bounds__(NTHREADS, 1) gram_kernel(GramParams p)
-{
-    extern __shared__ __align__(16) double smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm0 = (warp & 1) * WM, wn0 = (warp >> 1) * WN;
+struct GramTmaParams {
+    int ktiles; // 16-wide k steps
+    int64_t npair;
+    double *G;
+    int64_t ldg;
+    const int2 *tiles;
+    int ntiles;
+};
 
+__global__ void __launch_bounds__(NTHREADS, 1)
+gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment: the swizzle phase of a row is taken from address bits 7..9
+    uint8_t *smem = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
+    uint64_t *empty = full + STAGES;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], NCONSUMER_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp >= NCONSUMER_WARPS) {
+        // ---------------- producer warpgroup: gives its registers to the consumers ----------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == NCONSUMER_WARPS && lane == 0) {
+            int s = 0, phase = 0;
+            for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+                const int2 tt = p.tiles[tile];
+                const int m0 = tt.x * TM, n0 = tt.y * TN;
+                for (int kt = 0; kt < p.ktiles; ++kt) {
+                    mbar_wait(&empty[s], phase ^ 1);
+                    mbar_expect_tx(&full[s], STAGE_BYTES);
+                    uint8_t *As = smem + s * STAGE_BYTES;
+                    tma_load_2d(As, &tmap, kt * BK, m0, &full[s]);
+                    tma_load_2d(As + TILE_BYTES, &tmap, kt * BK, n0, &full[s]);
+                    if (++s == STAGES) {
+                        s = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers ----------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    const int wm0 = (warp & 1) * WM, wn0 = (warp >> 1) * WN;
+    const int g = lane >> 2, t = lane & 3;
+    int koff[BK / 4]; // swizzled position (in doubles) of this lane's k element inside a 16-double row
+#pragma unroll
+    for (int ks = 0; ks < BK / 4; ++ks) koff[ks] = (((4 * (t >> 1) + ks) ^ g) << 1) + (t & 1);
+
+    int s = 0, phase = 0;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
         const int2 tt = p.tiles[tile];
         const int64_t m0 = (int64_t)tt.x * TM, n0 = (int64_t)tt.y * TN;
-
         WarpAcc<WM, WN> acc;
         acc.zero();
-
-        auto load_stage = [&](int s, int kt) {
-            double *As = smem + s * STAGE_DOUBLES;
-            double *Bs = As + TM * PITCH_K;
-            load_rows_kmajor(As, p.X, p.ldx, m0, p.npair, kt * BK, tid);
-            load_rows_kmajor(Bs, p.X, p.ldx, n0, p.npair, kt * BK, tid);
-        };
-
-#pragma unroll
-        for (int s = 0; s < STAGES - 1; ++s) {
-            if (s < p.ktiles) load_stage(s, s);
-            cp_async_commit();
-        }
         for (int kt = 0; kt < p.ktiles; ++kt) {
-            cp_async_wait<STAGES - 2>();
-            __syncthreads();
-            const int nk = kt + STAGES - 1;
-            if (nk < p.ktiles) load_stage(nk % STAGES, nk);
-            cp_async_commit();
-            const double *As = smem + (kt % STAGES) * STAGE_DOUBLES;
-            const double *Bs = As + TM * PITCH_K;
-            warp_mma_stage<WM, WN, true, PITCH_K, PITCH_K>(acc, As, Bs, wm0, wn0, lane);
+            mbar_wait(&full[s], phase);
+            const double *As = reinterpret_cast<const double *>(smem + s * STAGE_BYTES);
+            const double *Bs = As + TILE_BYTES / 8;
+#pragma unroll
+            for (int ks = 0; ks < BK / 4; ++ks) {
+                double a[WM / 8], b[WN / 8];
+#pragma unroll
+                for (int i = 0; i < WM / 8; ++i) a[i] = As[(wm0 + 8 * i + g) * BK + koff[ks]];
+#pragma unroll
+                for (int j = 0; j < WN / 8; ++j) b[j] = Bs[(wn0 + 8 * j + g) * BK + koff[ks]];
+#pragma unroll
+                for (int i = 0; i < WM / 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < WN / 8; ++j) dmma884(acc.c[i][j][0], acc.c[i][j][1], a[i], b[j]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+            if (++s == STAGES) {
+                s = 0;
+                phase ^= 1;
+            }
         }
-        cp_async_wait<0>();
-        __syncthreads(); // all warps done with the ring before the next tile's prologue refills it
-
-        // epilogue: direct tile + mirrored tile (skipped on the diagonal, where the tile is complete)
-        const int g = lane >> 2, t = lane & 3;
+        // epilogue: direct tile + mirrored tile (diagonal tiles are complete by themselves)
         const bool offdiag = tt.x != tt.y;
 #pragma unroll
         for (int i = 0; i < WM / 8; ++i) {
@@ -102,13 +191,44 @@ __global__ void __launch_bounds__(NTHREADS, 1) gram_kernel(GramParams p)
     }
 }
 
-cudaError_t launch_gram(const GramParams &p, cudaStream_t s)
+// ---- host ---------------------------------------------------------------------------------------------
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode()
 {
-    // per device, so set on every launch (a few hundred ns)
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+} // namespace
+
+cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
+{
+    if (p.ntiles <= 0) return cudaSuccess;
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return cudaErrorNotSupported;
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2] = {(cuuint64_t)p.ktiles * BK, (cuuint64_t)p.npair};
+    const cuuint64_t gstride[1] = {(cuuint64_t)p.ldx * 8};
+    const cuuint32_t box[2] = {BK, 128};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double *>(p.X), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    if (p.ntiles <= 0) return cudaSuccess;
-    gram_kernel<<<p.ntiles, NTHREADS, SMEM_BYTES, s>>>(p);
+    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles};
+    const int grid = p.ntiles < num_sms ? p.ntiles : num_sms;
+    gram_kernel<<<grid, NTHREADS, SMEM_BYTES, s>>>(tmap, kp);
     return cudaGetLastError();
 }
 

@@ -16,9 +16,8 @@ struct GramParams {
     const int2 *tiles; // (ti, tj), ti >= tj, L2-friendly order
     int ntiles;
 };
-cudaError_t launch_gram(const GramParams &p, cudaStream_t s);
-// TMA + mbarrier, persistent (one CTA per SM); same tile list as launch_gram
-cudaError_t launch_gram_tma(const GramParams &p, int num_sms, cudaStream_t s);
+// TMA + mbarrier pipeline, persistent (one CTA per SM, grid = min(ntiles, num_sms))
+cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s);
 // host: fills the lower-triangular tile list for nt row tiles; returns count
 int64_t build_gram_tiles(int nt, int2 *out /* nt*(nt+1)/2 */);
 constexpr int GRAM_TILE = 128;

@@ -98,6 +98,13 @@ class Context:
         check(lib().qemb_ctx_launch_count(self._h, ctypes.byref(n)))
         return n.value
 
+    @property
+    def transfer_bytes(self) -> tuple[int, int]:
+        """(host->device, device->host) bytes this context has handed to the copy engines so far."""
+        a, b = c_i64(), c_i64()
+        check(lib().qemb_ctx_transfer_bytes(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
     def probe_dmma_tflops(self, n: int = 4096, k: int = 2048, iters: int = 5) -> float:
         v = c_dbl()
         check(lib().qemb_probe_dmma_tflops(self._h, c_i64(n), c_i64(k), c_int(iters), ctypes.byref(v)))

@@ -1,5 +1,5 @@
 // scripts/gram_variants.cu -- development aid: sweeps tile shapes of the K3 kernel on a B200.
-//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I quemb_b200/csrc scripts/gram_variants.cu -o gpurun_out/gram_variants
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I quemb_b200/csrc -I scripts scripts/gram_variants.cu quemb_b200/csrc/k3_gram.cu -lcuda -o gpurun_out/gram_variants
 #include <cstdio>
 #include <vector>
 #include "gram_impl.cuh"
@@ -46,13 +46,13 @@ void run_tma(const char *name, int64_t npair, int64_t naux, double *X, int64_t l
     GramParams p; p.X = X; p.ldx = ldx; p.ktiles = (int)((naux + 15) / 16); p.npair = npair; p.G = G; p.ldg = npair;
     p.tiles = dt; p.ntiles = (int)h.size();
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-    cudaError_t e = launch_gram_tma(p, sms, 0);
+    cudaError_t e = launch_gram(p, sms, 0);
     if (e != cudaSuccess) { printf("%-28s launch failed: %s\n", name, cudaGetErrorString(e)); return; }
     e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("%-28s run failed: %s\n", name, cudaGetErrorString(e)); return; }
     float best = 1e30f;
     for (int r = 0; r < 3; ++r) {
-        cudaEventRecord(e0); launch_gram_tma(p, sms, 0); cudaEventRecord(e1); cudaEventSynchronize(e1);
+        cudaEventRecord(e0); launch_gram(p, sms, 0); cudaEventRecord(e1); cudaEventSynchronize(e1);
         float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
     }
     const double alg = (double)naux * npair * (npair + 1);
@@ -94,5 +94,12 @@ int main(int argc, char **argv)
     run<GramCfg<128, 128, 64, 32, 16, 4, 1>>("128x128 w64x32 k16 s4 g8", npair, naux, X, ldx, G, 8);
     run<GramCfg<128, 128, 64, 32, 16, 4, 1>>("128x128 w64x32 k16 s4 g16", npair, naux, X, ldx, G, 16);
     run<GramCfg<256, 128, 64, 64, 16, 3, 1>>("256x128 w64x64 k16 s3", npair, naux, X, ldx, G, 6);
+    // independent CTAs per SM instead of one big one (barriers of different CTAs do not line up)
+    run<GramCfg<64, 128, 32, 64, 16, 3, 2>>("64x128 w32x64 k16 s3 x2 (4w)", npair, naux, X, ldx, G, 24);
+    run<GramCfg<128, 64, 64, 32, 16, 3, 2>>("128x64 w64x32 k16 s3 x2 (4w)", npair, naux, X, ldx, G, 12);
+    run<GramCfg<128, 64, 64, 32, 16, 4, 2>>("128x64 w64x32 k16 s4 x2 (4w)", npair, naux, X, ldx, G, 12);
+    run<GramCfg<128, 64, 64, 32, 32, 2, 2>>("128x64 w64x32 k32 s2 x2 (4w)", npair, naux, X, ldx, G, 12);
+    run<GramCfg<64, 64, 32, 32, 16, 4, 3>>("64x64 w32x32 k16 s4 x3 (4w)", npair, naux, X, ldx, G, 24);
+    run<GramCfg<64, 128, 32, 64, 16, 3, 2>>("64x128 w32x64 k16 s3 x2 g12", npair, naux, X, ldx, G, 12);
     return 0;
 }
