@@ -1158,6 +1158,7 @@ int contract_1st(qemb_workspace *w, const qemb_tensor *t, int64_t p0, int64_t p1
     p.Asrc = t->data.as<double>() + p0;
     p.lda = t->ldp;
     p.M = (int)w->mrows;
+    p.Mread = (int)(t->ldp - p0);
     p.acol = t->d_rcol.as<int>();
     p.brow = t->d_ridx.as<int>();
     p.TA = s.TA.as<double>();
@@ -1173,7 +1174,7 @@ int contract_1st(qemb_workspace *w, const qemb_tensor *t, int64_t p0, int64_t p1
         CU(cudaEventRecord(w->ev[0], cs));
         w->ev_valid[0] = true;
     }
-    CU(launch_gather_gemm(p, cs));
+    CU(launch_gather_gemm(p, w->ctx->num_sms, cs));
     w->ctx->launches += (p.ntiles > 0);
     if (w->ctx->timing) {
         CU(cudaEventRecord(w->ev[1], cs));
@@ -1197,6 +1198,7 @@ int contract_2nd(qemb_workspace *w)
     p.Asrc = w->Bint.as<double>();
     p.lda = w->ldp;
     p.M = (int)w->mrows;
+    p.Mread = (int)w->ldp;
     p.acol = s.pd.acol2;
     p.brow = s.pd.brow2;
     p.TA = s.TA.as<double>();
@@ -1208,7 +1210,7 @@ int contract_2nd(qemb_workspace *w)
     p.groups = s.pd.groups2;
     p.tiles = s.pd.tiles2;
     p.ntiles = s.pd.ntiles2;
-    CU(launch_gather_gemm(p, cs));
+    CU(launch_gather_gemm(p, w->ctx->num_sms, cs));
     w->ctx->launches += (p.ntiles > 0);
     if (w->ctx->timing) {
         CU(cudaEventRecord(w->ev[2], cs));

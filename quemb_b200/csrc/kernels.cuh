@@ -32,7 +32,8 @@ struct GatherGroup {
 struct GatherParams {
     const double *Asrc;
     int64_t lda;
-    int M; // rows (auxiliary slab), multiple of 2
+    int M;     // rows (auxiliary slab) that are computed and stored
+    int Mread; // rows that exist below Asrc in every source column (>= M, multiple of 16): tiles are fetched whole
     const int *acol;
     const int *brow;
     const double *TA;
@@ -45,7 +46,7 @@ struct GatherParams {
     const int4 *tiles; // (group, m tile, n tile, unused)
     int ntiles;
 };
-cudaError_t launch_gather_gemm(const GatherParams &p, cudaStream_t s);
+cudaError_t launch_gather_gemm(const GatherParams &p, int num_sms, cudaStream_t s);
 constexpr int GATHER_TILE_M = 128;
 constexpr int GATHER_TILE_N = 128;
 
