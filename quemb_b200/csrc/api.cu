@@ -76,6 +76,10 @@ struct qemb_ctx {
     int out_mode = 1;
     int num_sms = 148;
     int64_t h2d_bytes = 0, d2h_bytes = 0; // bytes handed to the copy engines (uploads / G transfers)
+    // host-bound G transfers whose host mirror has not finished yet (qemb_ctx_synchronize waits for them)
+    std::mutex out_mutex;
+    std::condition_variable out_cv;
+    int64_t out_pending = 0;
     // pinned bounce buffers for uploads out of pageable host memory
     void *bounce[2] = {nullptr, nullptr};
     cudaEvent_t bounce_free[2] = {nullptr, nullptr};
@@ -263,7 +267,18 @@ struct OutJob {
     std::condition_variable cv;
     int64_t remaining = 0; // outstanding mirror tasks + 1 while copy groups are still in flight
     bool active = false;   // this ticket travels as a triangle (wait on the job, not only on the event)
+    qemb_ctx *ctx = nullptr;
 };
+
+// called with job.m held, when job.remaining has just dropped to 0
+inline void job_finished(OutJob &job)
+{
+    job.cv.notify_all();
+    if (job.ctx) {
+        std::lock_guard<std::mutex> lk(job.ctx->out_mutex);
+        if (--job.ctx->out_pending == 0) job.ctx->out_cv.notify_all();
+    }
+}
 constexpr int OUT_RING = 4;
 
 inline void wait_job(OutJob &job)
@@ -302,6 +317,8 @@ struct qemb_workspace {
     // timing
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t evs[2] = {nullptr, nullptr};
+    cudaEvent_t ev2s = nullptr; // start of K2a (its launch follows host-side plan building, unlike the others)
+    bool ev2s_valid = false;
     bool ev_valid[5] = {false, false, false, false, false};
     bool evs_valid = false;
 };
@@ -374,6 +391,10 @@ extern "C" int qemb_ctx_synchronize(qemb_ctx *c)
     CU(cudaStreamSynchronize(c->prep));
     CU(cudaStreamSynchronize(c->compute));
     CU(cudaStreamSynchronize(c->copy));
+    {   // host threads still mirroring a G that has landed
+        std::unique_lock<std::mutex> lk(c->out_mutex);
+        c->out_cv.wait(lk, [&] { return c->out_pending == 0; });
+    }
     return QEMB_OK;
 }
 
@@ -823,6 +844,7 @@ extern "C" int qemb_workspace_create(qemb_ctx *ctx, qemb_workspace **out)
     }
     for (int i = 0; i < 5; ++i) CU(cudaEventCreate(&w->ev[i]));
     for (int i = 0; i < 2; ++i) CU(cudaEventCreate(&w->evs[i]));
+    CU(cudaEventCreate(&w->ev2s));
     *out = w;
     return QEMB_OK;
 }
@@ -852,6 +874,7 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     }
     for (int i = 0; i < 5; ++i) cudaEventDestroy(w->ev[i]);
     for (int i = 0; i < 2; ++i) cudaEventDestroy(w->evs[i]);
+    cudaEventDestroy(w->ev2s);
     w->Bint.release();
     w->sym.release();
     for (auto &kv : w->gram_tiles) kv.second.first.release();
@@ -908,6 +931,40 @@ int upload_TA(qemb_workspace *w, const double *TA, int64_t ld)
 
 inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
+// Reorders a gather-GEMM tile list for the persistent kernel (CTA c runs tiles c, c + nsm, c + 2 nsm, ...):
+// tiles are dealt to the CTAs in serpentine order of decreasing cost, so every CTA gets the same amount of
+// tensor-pipe work, and each CTA alternates its expensive (many live columns: tensor bound) and cheap (few live
+// columns: bound by the A-operand traffic) tiles, odd CTAs starting with a cheap one, so the two kinds overlap
+// in time instead of leaving an HBM-bound tail of small tiles.
+void balance_tiles(int4 *tiles, const std::vector<float> &cost, int64_t n, int nsm)
+{
+    if (n <= nsm || nsm <= 1) return;
+    std::vector<int32_t> order((size_t)n);
+    for (int64_t i = 0; i < n; ++i) order[(size_t)i] = (int32_t)i;
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost[(size_t)a] > cost[(size_t)b]; });
+    const int64_t rounds = (n + nsm - 1) / nsm;
+    std::vector<int4> out((size_t)n);
+    std::vector<int32_t> mine;
+    for (int c = 0; c < nsm; ++c) {
+        mine.clear();
+        for (int64_t r = 0; r < rounds; ++r) {
+            const int64_t full = (r + 1) * nsm <= n ? nsm : n - r * nsm; // tiles in this round
+            const int64_t slot = (r & 1) && full == nsm ? nsm - 1 - c : c;
+            if (slot < full) mine.push_back(order[(size_t)(r * nsm + slot)]);
+        }
+        // alternate large / small
+        const int64_t k = (int64_t)mine.size();
+        int64_t lo = 0, hi = k - 1;
+        bool take_big = (c & 1) == 0;
+        for (int64_t q = 0; q < k; ++q) {
+            const int32_t t = take_big ? mine[(size_t)lo++] : mine[(size_t)hi--];
+            take_big = !take_big;
+            out[(size_t)(q * nsm + c)] = tiles[t];
+        }
+    }
+    std::copy(out.begin(), out.end(), tiles);
+}
+
 // K2a tables: depend only on the lists
 int build_plan2(qemb_workspace *w)
 {
@@ -932,6 +989,7 @@ int build_plan2(qemb_workspace *w)
     }
     int64_t bo = 0, nt = 0;
     double f2 = 0;
+    std::vector<float> cost((size_t)ntiles);
     for (int64_t a = 0; a < nmo; ++a) {
         const int K = (int)(s.aptr[a + 1] - s.aptr[a]), N = (int)(nmo - a);
         grp[a] = GatherGroup{K, N, (int)s.aptr[a], (int)bo};
@@ -942,9 +1000,14 @@ int build_plan2(qemb_workspace *w)
         bo += N;
         const int ntn = (N + GATHER_TILE_N - 1) / GATHER_TILE_N;
         for (int m = 0; m < mtiles; ++m)
-            for (int n = 0; n < ntn; ++n) tiles[nt++] = make_int4((int)a, m, n, 0);
+            for (int n = 0; n < ntn; ++n) {
+                const int nv = std::min(GATHER_TILE_N, N - n * GATHER_TILE_N);
+                cost[(size_t)nt] = (float)((K + 15) / 16) * (2.f + (float)((nv + 7) / 8));
+                tiles[nt++] = make_int4((int)a, m, n, 0);
+            }
         f2 += 2.0 * (double)K * (double)N;
     }
+    balance_tiles(tiles, cost, nt, w->ctx->num_sms);
     s.work[1] = f2 * (double)w->naux;                               // F_K2a
     s.work[5] = 8.0 * (double)w->naux * ((double)nA + (double)npair); // Bytes_K2a
     w->ctx->h2d_bytes += (int64_t)total;
@@ -1000,6 +1063,7 @@ int build_plan1(qemb_workspace *w, const qemb_tensor *t)
     }
     int64_t gi = 0, nt = 0;
     double f1 = 0;
+    std::vector<float> cost((size_t)ntiles);
     std::vector<uint8_t> col_touched; // U_f of SURVEY 8(d): distinct unique columns read
     col_touched.assign((size_t)std::max<int64_t>(t->n_unique, 1), 0);
     int64_t U = 0;
@@ -1010,7 +1074,11 @@ int build_plan1(qemb_workspace *w, const qemb_tensor *t)
         grp[gi] = GatherGroup{K, N, (int)t->rptr[mu], (int)tptr[mu]};
         const int ntn = (N + GATHER_TILE_N - 1) / GATHER_TILE_N;
         for (int m = 0; m < mtiles; ++m)
-            for (int n = 0; n < ntn; ++n) tiles[nt++] = make_int4((int)gi, m, n, 0);
+            for (int n = 0; n < ntn; ++n) {
+                const int nv = std::min(GATHER_TILE_N, N - n * GATHER_TILE_N);
+                cost[(size_t)nt] = (float)((K + 15) / 16) * (2.f + (float)((nv + 7) / 8));
+                tiles[nt++] = make_int4((int)gi, m, n, 0);
+            }
         ++gi;
         f1 += 2.0 * (double)K * (double)N;
         for (int64_t k = t->rptr[mu]; k < t->rptr[mu + 1]; ++k)
@@ -1019,6 +1087,7 @@ int build_plan1(qemb_workspace *w, const qemb_tensor *t)
                 ++U;
             }
     }
+    balance_tiles(tiles, cost, nt, w->ctx->num_sms);
     s.work[0] = f1 * (double)w->naux;                                                          // F_K1
     s.work[4] = 8.0 * (double)w->naux * ((double)U + (double)nA) + 8.0 * (double)nao * (double)nmo; // Bytes_K1
     w->ctx->h2d_bytes += (int64_t)total;
@@ -1210,6 +1279,10 @@ int contract_2nd(qemb_workspace *w)
     p.groups = s.pd.groups2;
     p.tiles = s.pd.tiles2;
     p.ntiles = s.pd.ntiles2;
+    if (w->ctx->timing) {
+        CU(cudaEventRecord(w->ev2s, cs));
+        w->ev2s_valid = true;
+    }
     CU(launch_gather_gemm(p, w->ctx->num_sms, cs));
     w->ctx->launches += (p.ntiles > 0);
     if (w->ctx->timing) {
@@ -1302,6 +1375,7 @@ int gram_ws(qemb_workspace *w)
 void reset_events(qemb_workspace *w)
 {
     for (int i = 0; i < 5; ++i) w->ev_valid[i] = false;
+    w->ev2s_valid = false;
     w->evs_valid = false;
 }
 
@@ -1404,7 +1478,7 @@ void CUDART_CB mirror_callback(void *arg)
     {
         std::lock_guard<std::mutex> lk(job->m);
         job->remaining += ntasks - (cb->last ? 1 : 0);
-        if (job->remaining == 0) job->cv.notify_all();
+        if (job->remaining == 0) job_finished(*job);
     }
     double *out = cb->out;
     const int64_t ld = cb->ld, n = cb->n, c0 = cb->c0, c1 = cb->c1;
@@ -1413,7 +1487,7 @@ void CUDART_CB mirror_callback(void *arg)
         host_pool().submit([=] {
             mirror_block(out, ld, c0, c1, r0, r1);
             std::lock_guard<std::mutex> lk(job->m);
-            if (--job->remaining == 0) job->cv.notify_all();
+            if (--job->remaining == 0) job_finished(*job);
         });
     }
     delete cb;
@@ -1434,6 +1508,9 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         std::lock_guard<std::mutex> lk(job.m);
         job.remaining = 1;
         job.active = true;
+        job.ctx = w->ctx;
+        std::lock_guard<std::mutex> lk2(w->ctx->out_mutex);
+        w->ctx->out_pending += 1;
     }
     const int64_t target = 64ll << 20;
     for (int64_t c0 = 0; c0 < n;) {
@@ -1450,6 +1527,7 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
             delete cb;
             std::lock_guard<std::mutex> lk(job.m);
             job.remaining = 0; // nothing will ever signal this job
+            job_finished(job);
             CU(e);
         }
         c0 = c1;
@@ -1526,6 +1604,7 @@ extern "C" int qemb_fragment_times(const qemb_workspace *w, float *ms5)
     if (w->evs_valid) CU(cudaEventElapsedTime(&ms5[0], w->evs[0], w->evs[1]));
     for (int i = 0; i < 4; ++i)
         if (w->ev_valid[i] && w->ev_valid[i + 1]) CU(cudaEventElapsedTime(&ms5[i + 1], w->ev[i], w->ev[i + 1]));
+    if (w->ev2s_valid && w->ev_valid[2]) CU(cudaEventElapsedTime(&ms5[2], w->ev2s, w->ev[2]));
     return QEMB_OK;
 }
 

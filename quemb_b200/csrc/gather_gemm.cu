@@ -15,18 +15,22 @@
 //
 // The auxiliary index P is the GEMM's m dimension: it is contiguous in HBM in the source columns and in
 // the output columns.  Persistent kernel, one CTA per SM, warp specialised like K3 (k3_gram.cu):
-//   * producer warpgroup (4 warps, 56 registers each after setmaxnreg; the consumers take 224):
+//   * producer warpgroup (4 warps, 88 registers each after setmaxnreg; the consumers take 208):
 //       - A tile: 16 gathered columns x 128 rows per stage = 16 bulk copies of 1 KB (cp.async.bulk, the 1-D
 //         TMA path, one per lane) into As[k][m] (pitch 132), completing on the stage's "full" mbarrier;
 //       - B tile: the element-wise double gather TA[brow[k], bcol[n]] out of the L1/L2-resident TA with plain
 //         loads + st.shared into Bs[n][k] (pitch 20); the four warps arrive on the same mbarrier.
 //     The producers run up to STAGES stages ahead, across tile boundaries, so index loads, the gather
 //     latency, the pipeline fill of the next tile and the epilogue of the previous one are all hidden.
-//   * eight consumer warps (64 x 32 register tiles of DMMA.8x8x4 accumulators) wait on "full", read
-//     fragments with conflict-free 64-bit LDS and release the stage through "empty".  No CTA-wide barrier.
-//   * n quantisation: the 16 column blocks (of 8) of a tile are dealt round-robin to the four n-warps, and a
-//     warp skips the blocks beyond the group's N, so a ragged tile costs ceil(N/32)*32 columns on every
-//     warp instead of 128 (K2a groups have N = 1..nmo: 61 % -> 87 % useful work at nmo = 220).
+//   * eight consumer warps (32 x 64 register tiles of DMMA.8x8x4 accumulators, 4 m-warps x 2 n-warps) wait on
+//     "full", read fragments with conflict-free 64-bit LDS and release the stage through "empty".  No
+//     CTA-wide barrier.
+//   * n quantisation: the 16 column blocks (of 8) of a tile alternate between the two n-warps, which sit on the
+//     same scheduler; a warp runs the stage body specialised for its number of live blocks (8 code paths,
+//     warp-uniform branch), so a ragged tile costs ceil(N/8)*8 columns of tensor-pipe time instead of 128
+//     (K2a groups have N = 1..nmo: 61 % -> 96 % useful work at nmo = 220; K1: 61 % -> 93 %).
+#include <cstdlib>
+
 #include "dmma_core.cuh"
 #include "kernels.cuh"
 
@@ -44,7 +48,7 @@ constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * STAGES * 8 + 16;
 constexpr int NCONSUMER_WARPS = 8;
 constexpr int NPRODUCER_WARPS = 4;
 constexpr int NTHREADS = 32 * (NCONSUMER_WARPS + NPRODUCER_WARPS);
-constexpr int WM = 64, WN = 32;
+constexpr int WM = 32, WN = 64; // consumer warp tile: 4 m-warps x 2 n-warps
 
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
 {
@@ -83,6 +87,27 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, int bytes,
 }
 } // namespace
 
+// One BK = 16 stage of a consumer warp with JV live column blocks of 8.  (A predicated form -- `if (j < jv)`
+// around every DMMA -- costs a full stage whatever jv is: a predicated-off DMMA still takes its slot in the
+// pipe; measured, K1 4.3 ms with and without the skips.)  JV is warp-uniform, so the dispatch is a plain branch.
+template <int JV>
+__device__ __forceinline__ void consumer_stage(WarpAcc<WM, WN> &acc, const double *__restrict__ As,
+                                               const double *__restrict__ Bs, int wm0, int wni, int g, int t)
+{
+#pragma unroll
+    for (int ks = 0; ks < BK / 4; ++ks) {
+        double a[WM / 8], b[JV];
+#pragma unroll
+        for (int i = 0; i < WM / 8; ++i) a[i] = As[(4 * ks + t) * PA + wm0 + 8 * i + g];
+#pragma unroll
+        for (int j = 0; j < JV; ++j) b[j] = Bs[(8 * (2 * j + wni) + g) * PB + 4 * ks + t];
+#pragma unroll
+        for (int j = 0; j < JV; ++j)
+#pragma unroll
+            for (int i = 0; i < WM / 8; ++i) dmma884(acc.c[i][j][0], acc.c[i][j][1], a[i], b[j]);
+    }
+}
+
 __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -102,7 +127,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
 
     if (warp >= NCONSUMER_WARPS) {
         // ------------------------------------ producers ------------------------------------------
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
         const int pw = warp - NCONSUMER_WARPS; // 0..3
         const int ptid = tid - 32 * NCONSUMER_WARPS; // 0..127
         const int kk = ptid & 15;                    // this thread's k inside a stage (B gather)
@@ -126,13 +151,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
                 const int n = nb + 8 * r;
                 boff[r] = n < nvalid ? bcol[n] * (int)p.ldta : -1;
             }
+            // software pipeline: the indices of stage kt+1 and the TA values of stage kt are loaded BEFORE the
+            // wait for the stage's buffer, so their latency overlaps the wait (or, when the consumers are
+            // starved, only one load latency + the stores sits between two stages)
+            const int nfill = ((nvalid + 7) >> 3) << 3; // consumers never use column blocks beyond this
+            int rr = (kk < K) ? brow[kk] : -1;
+            int ac = (pw == 0 && lane < min(BK, K)) ? acol[lane] : -1;
             for (int kt = 0; kt < ktiles; ++kt) {
                 const int k0 = kt * BK;
                 const int nk = min(BK, K - k0);
-                // index loads before the wait: they overlap the wait for the stage
-                const int64_t rr = kk < nk ? brow[k0 + kk] : -1;
-                int64_t ac = -1;
-                if (pw == 0 && lane < nk) ac = acol[k0 + lane];
+                double v[TN / 8];
+#pragma unroll
+                for (int r = 0; r < TN / 8; ++r) {
+                    v[r] = 0.0;
+                    if (rr >= 0 && boff[r] >= 0 && !(p.debug & 1)) v[r] = __ldg(p.TA + rr + boff[r]);
+                }
+                const int k1 = k0 + BK;
+                const int rr_next = (k1 + kk < K) ? brow[k1 + kk] : -1;
+                int ac_next = -1;
+                if (pw == 0 && k1 + lane < K && lane < BK) ac_next = acol[k1 + lane];
                 mbar_wait(&empty[s], phase ^ 1);
                 uint8_t *stage = smem + s * STAGE_BYTES;
                 double *As = reinterpret_cast<double *>(stage);
@@ -145,20 +182,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         __syncwarp();
                     }
-                    if (lane == 0) mbar_expect_tx(&full[s], nk * rows * 8);
+                    if (lane == 0) mbar_expect_tx(&full[s], (p.debug & 2) ? 0 : nk * rows * 8);
                     __syncwarp();
-                    if (lane < nk) bulk_load(As + lane * PA, p.Asrc + ac * p.lda + m0, rows * 8, &full[s]);
+                    if (lane < nk && !(p.debug & 2)) bulk_load(As + lane * PA, p.Asrc + (int64_t)ac * p.lda + m0, rows * 8, &full[s]);
                 }
-                // B gather: Bs[n][k] = TA[brow[k], bcol[n]]
+                // B tile: Bs[n][k] = TA[brow[k], bcol[n]]
 #pragma unroll
                 for (int r = 0; r < TN / 8; ++r) {
                     const int n = nb + 8 * r;
-                    double v = 0.0;
-                    if (rr >= 0 && boff[r] >= 0) v = __ldg(p.TA + rr + boff[r]);
-                    Bs[n * PB + kk] = v;
+                    if (n < nfill) Bs[n * PB + kk] = v[r];
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&full[s]);
+                rr = rr_next;
+                ac = ac_next;
                 if (++s == STAGES) {
                     s = 0;
                     phase ^= 1;
@@ -169,9 +206,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
     }
 
     // -------------------------------------- consumers ------------------------------------------------
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
-    const int wmi = warp & 1, wni = warp >> 1;
-    const int wm0 = wmi * WM;
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+    // warps w and w + 4 share a scheduler: they take the same rows and the two column-block parities, so every
+    // scheduler sees ceil(N/8) blocks in total whatever N is
+    const int wm0 = (warp & 3) * WM, wni = warp >> 2;
     const int g = lane >> 2, t = lane & 3;
 
     int s = 0, phase = 0;
@@ -181,20 +219,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
         const int m0 = tt.y * TM, n0 = tt.z * TN;
         const int nvalid = min(TN, grp.N - n0);
         const int ktiles = (grp.K + BK - 1) / BK;
-        // column blocks (of 8) are dealt round-robin to the four n-warps: block index = 4 j + wni
-        const int nblocks = (nvalid + 7) >> 3;
-        const int jv = nblocks > wni ? (nblocks - wni + 3) >> 2 : 0; // valid j of this warp
-        const int mvalid = min(TM, p.M - m0) - wm0;                  // valid rows of this warp's half
-        const int iv = mvalid > 0 ? min(WM / 8, (mvalid + 7) >> 3) : 0;
-        // output columns of this thread: n = 8 (4 j + wni) + 2 t + e
-        int cc[WN / 8][2];
-#pragma unroll
-        for (int j = 0; j < WN / 8; ++j)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int n = 8 * (4 * j + wni) + 2 * t + e;
-                cc[j][e] = n < nvalid ? p.ccol[grp.b_off + n0 + n] : -1;
-            }
+        const int nblocks = (nvalid + 7) >> 3;      // live column blocks of 8
+        const int jv = (nblocks - wni + 1) >> 1;    // ... of which this warp owns blocks 2 j + wni
 
         WarpAcc<WM, WN> acc;
         acc.zero();
@@ -202,20 +228,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
             mbar_wait(&full[s], phase);
             const double *As = reinterpret_cast<const double *>(smem + s * STAGE_BYTES);
             const double *Bs = reinterpret_cast<const double *>(smem + s * STAGE_BYTES + A_BYTES);
-#pragma unroll
-            for (int ks = 0; ks < BK / 4; ++ks) {
-                double a[WM / 8], b[WN / 8];
-#pragma unroll
-                for (int i = 0; i < WM / 8; ++i) a[i] = As[(4 * ks + t) * PA + wm0 + 8 * i + g];
-#pragma unroll
-                for (int j = 0; j < WN / 8; ++j) b[j] = Bs[(8 * (4 * j + wni) + g) * PB + 4 * ks + t];
-#pragma unroll
-                for (int j = 0; j < WN / 8; ++j)
-                    if (j < jv) {
-#pragma unroll
-                        for (int i = 0; i < WM / 8; ++i)
-                            if (i < iv) dmma884(acc.c[i][j][0], acc.c[i][j][1], a[i], b[j]);
-                    }
+            switch (jv) {
+#define GG_CASE(J) case J: consumer_stage<J>(acc, As, Bs, wm0, wni, g, t); break;
+                GG_CASE(8) GG_CASE(7) GG_CASE(6) GG_CASE(5) GG_CASE(4) GG_CASE(3) GG_CASE(2) GG_CASE(1)
+#undef GG_CASE
+            default: break;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);
@@ -225,13 +242,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
             }
         }
 
-        // epilogue: scatter the columns (K == 0 groups write zeros, like the reference's zero init)
+        // epilogue: scatter the columns (K == 0 groups write zeros, like the reference's zero init); rows beyond
+        // M were computed on whatever the A stage held and are dropped here
+        const int *ccol = p.ccol + grp.b_off + n0;
 #pragma unroll
         for (int j = 0; j < WN / 8; ++j) {
+            if (j >= jv) break;
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
-                if (cc[j][e] < 0) continue;
-                double *dst = p.C + (int64_t)cc[j][e] * p.ldc;
+                const int n = 8 * (2 * j + wni) + 2 * t + e;
+                if (n >= nvalid) continue;
+                double *dst = p.C + (int64_t)ccol[n] * p.ldc;
 #pragma unroll
                 for (int i = 0; i < WM / 8; ++i) {
                     const int row = m0 + wm0 + 8 * i + g;
@@ -249,7 +270,10 @@ cudaError_t launch_gather_gemm(const GatherParams &p, int num_sms, cudaStream_t 
     if (e != cudaSuccess) return e;
     if (p.ntiles <= 0) return cudaSuccess;
     const int grid = p.ntiles < num_sms ? p.ntiles : num_sms;
-    gather_gemm_kernel<<<grid, NTHREADS, SMEM_BYTES, s>>>(p);
+    GatherParams q = p;
+    static const int dbg = getenv("QEMB_GG_DEBUG") ? atoi(getenv("QEMB_GG_DEBUG")) : 0;
+    q.debug = dbg;
+    gather_gemm_kernel<<<grid, NTHREADS, SMEM_BYTES, s>>>(q);
     return cudaGetLastError();
 }
 

@@ -45,6 +45,7 @@ struct GatherParams {
     const GatherGroup *groups;
     const int4 *tiles; // (group, m tile, n tile, unused)
     int ntiles;
+    int debug; // development only (QEMB_GG_DEBUG): 1 = skip the TA gather, 2 = skip the A copies; results are garbage
 };
 cudaError_t launch_gather_gemm(const GatherParams &p, int num_sms, cudaStream_t s);
 constexpr int GATHER_TILE_M = 128;

@@ -568,7 +568,7 @@ def transform_integral(
         ctypes.byref(ticket)))
     ws.last_ticket = ticket.value
     if synchronize:
-        ctx.synchronize()
+        ws.wait_output(ticket.value)  # copies AND the host-side mirror of the upper triangle
     return out
 
 
