@@ -94,6 +94,15 @@ void qemb_metric_destroy(qemb_metric *);
  * device copy; afterwards qemb_fragment_transform skips the per-fragment solve (cpp:615). */
 int qemb_tensor_whiten(qemb_tensor *, const qemb_metric *);
 int qemb_tensor_is_whitened(const qemb_tensor *, int *flag);
+/* Aux-sharded staging (oversize fragments): `slab` is a tensor created with naux = the number of
+ * auxiliary rows this device owns; the call uploads columns [col0, col0+ncols) of the FULL-naux host matrix
+ * (rows >= p_begin + slab naux never travel), solves them against L in a scratch buffer and keeps rows
+ * [p_begin, p_begin + slab naux) -- the slab of L^-1 (P|mu nu) -- so no device ever holds all of (P|mu nu).
+ * Marks the slab whitened; qemb_fragment_transform on it (metric NULL) returns the slab's PARTIAL (ij|kl),
+ * to be summed over the devices (NCCL reduce).  p_begin must be a multiple of 16. */
+int qemb_tensor_upload_whitened_rows(qemb_tensor *slab, const qemb_metric *, const double *host, int64_t ld_host,
+                                     int64_t col0, int64_t ncols, int64_t p_begin);
+int qemb_tensor_release_scratch(qemb_tensor *);
 /* device -> device copy of the data (and whitened flag) between two tensors built from the same lists
  * (keeps a raw copy around when the same molecule is transformed repeatedly) */
 int qemb_tensor_copy_data(qemb_tensor *dst, const qemb_tensor *src);

@@ -101,6 +101,8 @@ _SIGS = {
     ),
     "qemb_fragment_wait_output": (c_int, [c_p, c_i64]),
     "qemb_tensor_copy_data": (c_int, [c_p, c_p]),
+    "qemb_tensor_upload_whitened_rows": (c_int, [c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i64]),
+    "qemb_tensor_release_scratch": (c_int, [c_p]),
     "qemb_fragment_work": (c_int, [c_p, c_p, c_p]),
     "qemb_ctx_set_timing": (c_int, [c_p, c_int]),
     "qemb_ctx_set_output_mode": (c_int, [c_p, c_int]),

@@ -219,6 +219,7 @@ struct qemb_tensor {
     std::vector<int64_t> rptr, ridx, rcol; // exch_reachable lists + column of every entry (cpp:260-279)
     std::vector<int64_t> uptr, uidx;       // exch_reachable_unique (hpp:149-162)
     DevBuf data, d_rcol, d_ridx;           // FP64 ldp x n_unique ; int32 copies of rcol / ridx
+    DevBuf scratch;                        // column chunk being whitened (qemb_tensor_upload_whitened_rows)
     bool whitened = false;
 };
 
@@ -637,6 +638,7 @@ extern "C" void qemb_tensor_destroy(qemb_tensor *t)
     t->data.release();
     t->d_rcol.release();
     t->d_ridx.release();
+    t->scratch.release();
     delete t;
 }
 
@@ -767,6 +769,55 @@ extern "C" int qemb_tensor_whiten(qemb_tensor *t, const qemb_metric *m)
     t->ctx->launches += 1;
     CU(cudaStreamSynchronize(t->ctx->compute));
     t->whitened = true;
+    return QEMB_OK;
+}
+
+// One column chunk of an AUXILIARY ROW SLAB of the whitened tensor, without ever holding the full
+// (P|mu nu) on this device: the chunk (all naux rows, `ncols` pair columns) is uploaded into scratch,
+// solved against L there (rows >= p_end are not needed by forward substitution and never travel) and
+// only rows [p_begin, p_begin + slab->naux) are kept.
+extern "C" int qemb_tensor_upload_whitened_rows(qemb_tensor *t, const qemb_metric *m, const double *host,
+                                                int64_t ld_host, int64_t col0, int64_t ncols, int64_t p_begin)
+{
+    REQ(t && m && (host || ncols == 0), "null argument");
+    REQ(t->ctx == m->ctx, "tensor and metric live on different contexts");
+    REQ(col0 >= 0 && ncols >= 0 && col0 + ncols <= t->n_unique, "column range outside the tensor");
+    REQ(p_begin >= 0 && p_begin % 16 == 0 && p_begin + t->naux <= m->naux, "bad auxiliary slab");
+    REQ(ld_host >= m->naux, "ld_host < naux of the metric");
+    if (ncols == 0) return QEMB_OK;
+    DeviceGuard g(t->ctx->device);
+    qemb_ctx *c = t->ctx;
+    cudaStream_t s = c->compute;
+    const int64_t p_end = p_begin + t->naux;
+    const int64_t mrows = round_up(p_end, 16);
+    const int64_t lds = m->naux_pad;
+    TRY(t->scratch.reserve((size_t)lds * (size_t)ncols * 8));
+    double *S = t->scratch.as<double>();
+    CU(cudaMemsetAsync(S, 0, (size_t)lds * (size_t)ncols * 8, s));
+    TRY(upload_2d(c, S, (size_t)lds * 8, host, (size_t)ld_host * 8, (size_t)p_end * 8, (size_t)ncols, s));
+    TrsmParams p;
+    p.L = m->L.as<double>();
+    p.ldl = m->naux_pad;
+    p.Dinv = m->Dinv.as<double>();
+    p.nblocks = m->nblocks;
+    p.X = S;
+    p.ldx = lds;
+    p.ncol = ncols;
+    CU(launch_trsm_rows(p, (int)mrows, s));
+    c->launches += 1;
+    CU(cudaMemcpy2DAsync(t->data.as<double>() + col0 * t->ldp, (size_t)t->ldp * 8, S + p_begin, (size_t)lds * 8,
+                         (size_t)t->naux * 8, (size_t)ncols, cudaMemcpyDeviceToDevice, s));
+    CU(cudaStreamSynchronize(s));
+    t->whitened = true;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_release_scratch(qemb_tensor *t)
+{
+    REQ(t, "null tensor");
+    DeviceGuard g(t->ctx->device);
+    CU(cudaStreamSynchronize(t->ctx->compute));
+    t->scratch.release();
     return QEMB_OK;
 }
 

@@ -350,6 +350,33 @@ class SemiSparseSym3DTensor:
         m = _metric_for(L_PQ, self.ctx)
         check(lib().qemb_tensor_whiten(self._h, m._h))
 
+    @classmethod
+    def whitened_slab(cls, unique_dense_data: np.ndarray, shape, exch_reachable, L_PQ, p_range: tuple[int, int],
+                      *, ctx: Context | None = None, chunk_cols: int = 8192) -> "SemiSparseSym3DTensor":
+        """Rows ``[p_begin, p_end)`` of ``L^-1 (P|mu nu)`` as a tensor of its own (aux-sharded fragments,
+        SURVEY 8e): the host matrix is streamed through the device in column chunks, solved against the
+        metric there, and only the slab's rows stay resident, so a rank never holds all of (P|mu nu).
+        Transforms on the result (metric ``None``) give the slab's partial (ij|kl)."""
+        naux, nao, _ = (int(x) for x in shape)
+        p0, p1 = int(p_range[0]), int(p_range[1])
+        if not (0 <= p0 < p1 <= naux) or p0 % 16:
+            raise _lib.QembError("auxiliary slab must satisfy 0 <= p_begin < p_end <= naux, p_begin % 16 == 0")
+        t = cls((p1 - p0, nao, nao), exch_reachable, ctx=ctx)
+        d = np.asarray(unique_dense_data)
+        if d.shape != (naux, t._n_unique) or d.dtype != np.float64 or d.strides[0] != 8:
+            d = _f64(d, "unique_dense_data")
+            if d.shape != (naux, t._n_unique):
+                raise _lib.QembError(f"unique_dense_data has shape {d.shape}, expected {(naux, t._n_unique)}")
+        m = _metric_for(L_PQ, t.ctx)
+        ld = d.strides[1] // 8 if d.shape[1] > 1 else naux
+        for c0 in range(0, t._n_unique, chunk_cols):
+            nc = min(chunk_cols, t._n_unique - c0)
+            check(lib().qemb_tensor_upload_whitened_rows(t._h, m._h, c_p(d.ctypes.data + 8 * ld * c0), c_i64(ld),
+                                                         c_i64(c0), c_i64(nc), c_i64(p0)))
+        check(lib().qemb_tensor_release_scratch(t._h))
+        t.p_range = (p0, p1)
+        return t
+
     def copy_data_from(self, other: "SemiSparseSym3DTensor") -> None:
         """Device-to-device copy of the data of a tensor built from the same lists."""
         other._flush()

@@ -1,0 +1,151 @@
+"""Aux-sharded fragments: the auxiliary index P of ONE fragment is split over the ranks of a process group.
+
+BASELINE.json north_star: "only fragments whose B tensor exceeds one GPU shard the auxiliary index P and
+combine with an NCCL reduce-sum over NVLink" ("Oversize fragments").  The reference has no
+counterpart: its worker holds all of (P|mu nu) and (P|ij) in one address space
+(``src/quemb/molbe/eri_sparse_DF.py:621-631``).
+
+K1, K2a and K3 never mix auxiliary rows once the metric has been applied to (P|mu nu) (design option O1),
+
+    (ij|kl) = sum_P X[P,ij] X[P,kl] = sum_r  sum_{P in slab r} X[P,ij] X[P,kl],     X = (L^-1 M) o TA o TA,
+
+so rank r keeps rows ``[p_r, p_{r+1})`` of ``L^-1 (P|mu nu)`` (1/world of the tensor, staged through
+``SemiSparseSym3DTensor.whitened_slab``), runs the unchanged fragment kernels on its slab and the partial
+Gram matrices are summed onto the fragment's OWNER rank with one ``reduce`` per fragment (NCCL over
+NVLink/NVSwitch on the GPU box; owners rotate over the ranks so the device->host copy and the sink work of
+consecutive fragments land on different ranks).  The screening lists A(i) are computed redundantly by every
+rank from the same S_abs and TA with the same deterministic kernel, so every rank plans the same columns.
+
+The sum order differs from the single-GPU run: results agree to the 1e-10 budget, not bit for bit.
+"""
+
+from __future__ import annotations
+
+from typing import Callable, Sequence
+
+import numpy as np
+
+Sink = Callable[[int, np.ndarray], None]
+
+
+def aux_slabs(naux: int, world: int, align: int = 16) -> list[tuple[int, int]]:
+    """Split ``[0, naux)`` into ``world`` contiguous slabs whose interior bounds are multiples of ``align``
+    (the kernels' 16-row k tile).  Slabs differ by at most one tile; trailing slabs may be empty when
+    ``naux < align * world``."""
+    if naux <= 0 or world <= 0:
+        raise ValueError("naux and world must be positive")
+    ntile = -(-naux // align)
+    bounds = [min(naux, align * ((ntile * r) // world)) for r in range(world)] + [naux]
+    return [(bounds[r], bounds[r + 1]) for r in range(world)]
+
+
+def owner_of(k: int, world: int) -> int:
+    """Rank that receives the summed (ij|kl) of the k-th fragment of a sharded build."""
+    return k % world
+
+
+class AuxShardedBuilder:
+    """One rank's part of an aux-sharded all-fragment build.
+
+    ``dist`` is ``torch.distributed`` (initialised by the caller, backend ``nccl`` on GPUs); ``group`` the
+    process group the auxiliary index is split over.  The three hooks ``_stage_slab`` / ``_partial`` /
+    ``_to_host`` are the device side; the CPU tests replace them to exercise the orchestration over gloo.
+    """
+
+    def __init__(self, dist, device: int = 0, group=None):
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.device = device
+        self.slab: tuple[int, int] | None = None
+        self.tensor = None
+        self.screen = None
+        self.ws = None
+        self.ctx = None
+        self._G: list = [None, None]
+
+    # -- device side ------------------------------------------------------------------------------------
+    def _stage_slab(self, unique_dense_data, shape, exch_reachable, L_PQ, S_abs) -> None:
+        from . import eri_sparse_DF as q
+
+        self.ctx = q.default_context(self.device)
+        self.ws = q.Workspace(self.ctx)
+        metric = q.GPU_MatrixHandle(L_PQ, ctx=self.ctx)
+        self.tensor = q.SemiSparseSym3DTensor.whitened_slab(unique_dense_data, shape, exch_reachable, metric,
+                                                            self.slab, ctx=self.ctx)
+        del metric  # L is not needed after staging: the slab is already whitened
+        self.screen = q._ScreenHandle(np.asarray(S_abs), self.ctx)
+
+    def _buffer(self, k: int, n: int):
+        import torch
+
+        b = self._G[k & 1]
+        if b is None or b.numel() < n:
+            b = torch.empty(n, dtype=torch.float64, device=torch.device("cuda", self.device))
+            self._G[k & 1] = b
+        return b[:n]
+
+    def _partial(self, k: int, TA: np.ndarray, eps: float):
+        """Partial (ij|kl) of this rank's slab, as a flat device tensor of npair^2 doubles."""
+        from . import eri_sparse_DF as q
+
+        nmo = TA.shape[1]
+        npair = nmo * (nmo + 1) // 2
+        G = self._buffer(k, npair * npair)
+        q.transform_integral_device(self.tensor, TA, self.screen, None, eps, G.data_ptr(), npair, ws=self.ws)
+        self.ctx.synchronize()  # the collective runs on torch's stream: hand over a finished buffer
+        return G
+
+    def _to_host(self, G, npair: int) -> np.ndarray:
+        return G.cpu().numpy().reshape(npair, npair)
+
+    def _collective_done(self) -> None:
+        """NCCL's ``work.wait()`` only orders torch's stream after the collective; the library writes the
+        next partial on its own stream, so the host waits for torch's stream before the buffer is reused."""
+        import torch
+
+        torch.cuda.current_stream(self.device).synchronize()
+
+    # -- orchestration ----------------------------------------------------------------------------------
+    def stage(self, unique_dense_data, shape, exch_reachable, L_PQ, S_abs) -> None:
+        naux = int(shape[0])
+        self.slab = aux_slabs(naux, self.world)[self.rank]
+        if self.slab[1] <= self.slab[0]:
+            raise ValueError(f"rank {self.rank}: empty auxiliary slab (naux {naux} over {self.world} ranks)")
+        self._stage_slab(unique_dense_data, shape, exch_reachable, L_PQ, S_abs)
+
+    def build(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, sink: Sink | None = None,
+              indices: Sequence[int] | None = None) -> list[int]:
+        """Every rank calls this with the same arguments.  ``sink(i, G)`` runs on the owner rank of
+        fragment i only; returns the fragments this rank owned."""
+        idx = list(range(len(TAs))) if indices is None else list(indices)
+        owned: list[int] = []
+        pending = None  # (work handle, k, i, G, npair) of the previous fragment: its reduce overlaps our kernels
+        for k, i in enumerate(idx):
+            TA = np.asfortranarray(TAs[i], dtype=np.float64)
+            nmo = TA.shape[1]
+            npair = nmo * (nmo + 1) // 2
+            G = self._partial(k, TA, MO_coeff_epsilon)
+            if pending is not None:
+                self._finish(pending, sink, owned)
+            work = self.dist.reduce(G, dst=self._global_rank(owner_of(k, self.world)), op=self.dist.ReduceOp.SUM,
+                                    group=self.group, async_op=True)
+            pending = (work, k, i, G, npair)
+        if pending is not None:
+            self._finish(pending, sink, owned)
+        return owned
+
+    def _global_rank(self, group_rank: int) -> int:
+        if self.group is None:
+            return group_rank
+        return self.dist.get_global_rank(self.group, group_rank)
+
+    def _finish(self, pending, sink: Sink | None, owned: list[int]) -> None:
+        work, k, i, G, npair = pending
+        work.wait()
+        self._collective_done()
+        if owner_of(k, self.world) == self.rank:
+            owned.append(i)
+            if sink is not None:
+                sink(i, self._to_host(G, npair))

@@ -100,3 +100,86 @@ def test_reference_arm_prints_one_line_on_rank0_only():
     assert line["impl"] == "reference" and line["metric"] == "all_fragment_eri_build_time"
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["value"] > 0
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["higher_is_better"] is False
+
+
+def test_aux_slabs_cover_and_align():
+    from quemb_b200.sharded import aux_slabs, owner_of
+
+    for naux in (16, 72, 700, 2716, 9024):
+        for world in (1, 2, 3, 4, 8):
+            slabs = aux_slabs(naux, world)
+            assert slabs[0][0] == 0 and slabs[-1][1] == naux and len(slabs) == world
+            for (a0, a1), (b0, b1) in zip(slabs, slabs[1:]):
+                assert a1 == b0 and a0 <= a1
+            assert all(a % 16 == 0 for a, _ in slabs)
+            sizes = [b - a for a, b in slabs]
+            if naux >= 16 * world:
+                assert min(sizes) > 0 and max(sizes) - min(sizes) <= 16 + naux % 16
+    assert [owner_of(k, 4) for k in range(6)] == [0, 1, 2, 3, 0, 1]
+    with pytest.raises(ValueError):
+        aux_slabs(0, 2)
+
+
+SHARDED_WORKER = r"""
+import os, sys, json
+sys.path.insert(0, sys.argv[1])
+import numpy as np, scipy.linalg as sla
+import torch, torch.distributed as dist
+from oracle import oracle                      # CPU checker standing in for the device hooks
+from quemb_b200 import synthetic as syn
+from quemb_b200.sharded import AuxShardedBuilder, aux_slabs
+
+class CpuSlabBuilder(AuxShardedBuilder):
+    # the orchestration under test is the base class; only the three device hooks are replaced
+    def _stage_slab(self, M, shape, exch, L, S_abs):
+        p0, p1 = self.slab
+        W = sla.solve_triangular(L, M, lower=True)
+        self.W = np.asfortranarray(W[p0:p1]); self.exch = exch; self.S_abs = S_abs
+    def _partial(self, k, TA, eps):
+        G = oracle.transform_integral(self.W, self.exch, TA, self.S_abs, np.eye(self.W.shape[0]), eps)
+        return torch.from_numpy(np.ascontiguousarray(G).reshape(-1).copy())
+    def _to_host(self, G, npair):
+        return G.numpy().reshape(npair, npair)
+    def _collective_done(self):
+        pass
+
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+p = syn.make_chain_problem(n_units=6, ao_per_unit=6, n_end=1, naux=88, frag_halfwidth=1, n_bath=6, sigma=0.5, seed=5)
+b = AuxShardedBuilder.__new__(CpuSlabBuilder); AuxShardedBuilder.__init__(b, dist, device=0)
+b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+got = {}
+owned = b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: got.__setitem__(i, G.copy()))
+errs = {}
+for i, G in got.items():
+    ref = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, p.TAs[i], p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+    errs[i] = float(np.abs(G - ref).max())
+out = [None] * world
+dist.all_gather_object(out, {"rank": rank, "slab": b.slab, "owned": owned, "errs": errs})
+if rank == 0:
+    print(json.dumps({"ranks": out, "nfrag": len(p.TAs), "naux": p.naux}))
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_gloo_aux_sharded_reduce(tmp_path):
+    """N>1 path of the aux-sharded build on CPU: slabs, rotating owners, async reduce-sum, sink on the owner."""
+    script = tmp_path / "sharded_worker.py"
+    script.write_text(SHARDED_WORKER)
+    port = _free_port()
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), OMP_NUM_THREADS="2")
+        procs.append(subprocess.Popen([sys.executable, str(script), str(ROOT)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=240) for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    res = json.loads(outs[0][0].strip().splitlines()[-1])
+    r0, r1 = res["ranks"]
+    assert r0["slab"][0] == 0 and r0["slab"][1] == r1["slab"][0] and r1["slab"][1] == res["naux"]
+    assert sorted(r0["owned"] + r1["owned"]) == list(range(res["nfrag"]))
+    assert r0["owned"] == list(range(0, res["nfrag"], 2)) and r1["owned"] == list(range(1, res["nfrag"], 2))
+    errs = {**r0["errs"], **r1["errs"]}
+    assert len(errs) == res["nfrag"] and max(errs.values()) <= 1e-10, errs
