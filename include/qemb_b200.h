@@ -160,6 +160,18 @@ int qemb_fragment_transform(qemb_workspace *, const qemb_tensor *, const qemb_me
                             const qemb_screen *, const double *TA_host, int64_t ld, int64_t nao,
                             int64_t nmo, double eps, int64_t p_begin, int64_t p_end, double *out,
                             int64_t ld_out, int out_is_device, int64_t *ticket);
+/* `out` == NULL: (ij|kl) stays resident in the workspace (no device->host transfer); read it with
+ * qemb_fragment_get_G / qemb_fragment_G_dev or consume it in place with qemb_fragment_jk. */
+
+/* Consumer of the path, SURVEY 8f rank 1 -- scf.hf.dot_eri_dm(eri, dm, hermi=1) as called by get_veff
+ * (src/quemb/molbe/helper.py:28-69) and, through E2_i = sum_j D_ij (2J - K)_ij, the two-electron sum of
+ * update_ebe_hf (src/quemb/molbe/pfrag.py:368-389):  vj[i,j] = sum_kl (ij|kl) D[k,l],
+ * vk[i,k] = sum_jl (ij|kl) D[j,l] from the (ij|kl) of the last transform, read once where it lives in HBM.
+ * D, vj, vk: nmo x nmo column-major host matrices; D must be symmetric.  Synchronous. */
+int qemb_fragment_jk(qemb_workspace *, const double *D_host, int64_t ldd, double *vj_host, double *vk_host,
+                     int64_t ld_out);
+/* device time (ms) of the last qemb_fragment_jk and its algorithmic bytes (8 npair^2) */
+int qemb_fragment_jk_time(const qemb_workspace *, float *ms, double *bytes);
 /* blocks until the host output of the transform that returned `ticket` is complete */
 int qemb_fragment_wait_output(qemb_workspace *, int64_t ticket);
 

@@ -100,6 +100,8 @@ _SIGS = {
         [c_p, c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_dbl, c_i64, c_i64, c_p, c_i64, c_int, ctypes.POINTER(c_i64)],
     ),
     "qemb_fragment_wait_output": (c_int, [c_p, c_i64]),
+    "qemb_fragment_jk": (c_int, [c_p, c_p, c_i64, c_p, c_p, c_i64]),
+    "qemb_fragment_jk_time": (c_int, [c_p, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(c_dbl)]),
     "qemb_tensor_copy_data": (c_int, [c_p, c_p]),
     "qemb_tensor_upload_whitened_rows": (c_int, [c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i64]),
     "qemb_tensor_release_scratch": (c_int, [c_p]),

@@ -313,6 +313,10 @@ struct qemb_workspace {
     double *G_last = nullptr; // where the last K3 wrote
     int64_t G_last_ld = 0;
     bool have_G = false;
+    // J/K consumer (jk.cu)
+    DevBuf jk_in, jk_scratch, jk_out;
+    cudaEvent_t jk_ev[2] = {nullptr, nullptr};
+    float jk_ms = 0.f;
     // gram tile lists by number of row tiles
     std::map<int, std::pair<DevBuf, int>> gram_tiles;
     // timing
@@ -926,6 +930,11 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     for (int i = 0; i < 5; ++i) cudaEventDestroy(w->ev[i]);
     for (int i = 0; i < 2; ++i) cudaEventDestroy(w->evs[i]);
     cudaEventDestroy(w->ev2s);
+    for (auto &e : w->jk_ev)
+        if (e) cudaEventDestroy(e);
+    w->jk_in.release();
+    w->jk_scratch.release();
+    w->jk_out.release();
     w->Bint.release();
     w->sym.release();
     for (auto &kv : w->gram_tiles) kv.second.first.release();
@@ -1594,9 +1603,9 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
                                        int out_is_device, int64_t *ticket)
 {
     if (ticket) *ticket = -1;
-    REQ(w && t && sc && TA && out, "null argument");
+    REQ(w && t && sc && TA, "null argument");
     REQ(t->whitened || m, "a metric is required unless the tensor is whitened");
-    REQ(ld_out >= nmo * (nmo + 1) / 2, "ld_out < npair");
+    REQ(!out || ld_out >= nmo * (nmo + 1) / 2, "ld_out < npair");
     DeviceGuard g(w->ctx->device);
     reset_events(w);
     TRY(qemb_fragment_screen(w, sc, TA, ld, nao, nmo, eps, nullptr));
@@ -1604,8 +1613,9 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
     TRY(contract_2nd(w));
     if (!t->whitened) TRY(solve(w, m));
     Slot &s = w->slot[w->cur];
-    if (out_is_device) return gram(w, out, ld_out);
+    if (out && out_is_device) return gram(w, out, ld_out);
     TRY(gram_ws(w));
+    if (!out) return QEMB_OK; // resident: consumers (qemb_fragment_jk, qemb_fragment_get_G) read it in place
     const int gi = w->gi;
     // hand G to the copy stream; the compute stream moves on to the next fragment
     cudaEvent_t done;
@@ -1622,6 +1632,90 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
     w->g_copy_pending[gi] = true;
     w->ticket_gi[w->ticket & 1] = gi;
     if (ticket) *ticket = w->ticket;
+    return QEMB_OK;
+}
+
+// J/K of a symmetric density from the (ij|kl) the last transform left on the device (jk.cu).
+extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd, double *vj, double *vk, int64_t ldo)
+{
+    REQ(w && D && vj && vk && w->have_G, "null argument or no (ij|kl) on the device");
+    const Slot &s = w->slot[w->cur];
+    const int64_t nmo = s.nmo, npair = s.npair;
+    REQ(ldd >= nmo && ldo >= nmo, "leading dimension < nmo");
+    REQ(nmo <= jk_max_nmo(), "nmo too large for the J/K kernel");
+    double dmax = 0.0, amax = 0.0;
+    for (int64_t l = 0; l < nmo; ++l)
+        for (int64_t k = 0; k < nmo; ++k) {
+            dmax = std::max(dmax, std::fabs(D[k + ldd * l]));
+            amax = std::max(amax, std::fabs(D[k + ldd * l] - D[l + ldd * k]));
+        }
+    REQ(amax <= 1e-12 * std::max(dmax, 1e-300) || amax == 0.0, "density matrix must be symmetric (hermi=1)");
+    DeviceGuard g(w->ctx->device);
+    cudaStream_t cs = w->ctx->compute;
+    // chunk table: whole packed rows, at most jk_chunk_doubles() doubles per chunk
+    std::vector<int> crow{0};
+    {
+        int64_t used = 0;
+        for (int64_t k = 0; k < nmo; ++k) {
+            if (used + k + 1 > jk_chunk_doubles()) {
+                crow.push_back((int)k);
+                used = 0;
+            }
+            used += k + 1;
+        }
+        crow.push_back((int)nmo);
+    }
+    const int nch = (int)crow.size() - 1;
+    // inputs: D (nmo^2) | dpk (npair) | crow
+    const size_t oD = 0, oP = (size_t)nmo * nmo * 8, oC = oP + (size_t)npair * 8;
+    const size_t in_bytes = oC + crow.size() * 4;
+    std::vector<double> hin((in_bytes + 7) / 8);
+    for (int64_t l = 0; l < nmo; ++l)
+        for (int64_t k = 0; k < nmo; ++k) hin[k + nmo * l] = D[k + ldd * l];
+    for (int64_t k = 0; k < nmo; ++k)
+        for (int64_t l = 0; l <= k; ++l) hin[oP / 8 + k * (k + 1) / 2 + l] = (k == l ? 1.0 : 2.0) * D[k + ldd * l];
+    std::memcpy(reinterpret_cast<char *>(hin.data()) + oC, crow.data(), crow.size() * 4);
+    TRY(w->jk_in.reserve(in_bytes));
+    TRY(w->jk_scratch.reserve(((size_t)npair + 2 * (size_t)npair * nmo) * 8));
+    TRY(w->jk_out.reserve(2 * (size_t)nmo * nmo * 8));
+    CU(cudaMemcpyAsync(w->jk_in.p, hin.data(), in_bytes, cudaMemcpyHostToDevice, cs));
+    w->ctx->h2d_bytes += (int64_t)in_bytes;
+    JkParams p;
+    p.G = w->G_last;
+    p.ldg = w->G_last_ld;
+    p.npair = npair;
+    p.nmo = (int)nmo;
+    p.D = reinterpret_cast<const double *>(static_cast<char *>(w->jk_in.p) + oD);
+    p.dpk = reinterpret_cast<const double *>(static_cast<char *>(w->jk_in.p) + oP);
+    p.crow = reinterpret_cast<const int *>(static_cast<char *>(w->jk_in.p) + oC);
+    p.nchunks = nch;
+    p.Jp = w->jk_scratch.as<double>();
+    p.R1 = p.Jp + npair;
+    p.R2 = p.R1 + npair * nmo;
+    double *Jd = w->jk_out.as<double>(), *Kd = Jd + nmo * nmo;
+    for (auto &e : w->jk_ev)
+        if (!e) CU(cudaEventCreate(&e));
+    CU(cudaEventRecord(w->jk_ev[0], cs));
+    CU(launch_jk(p, Jd, Kd, nmo, w->ctx->num_sms, cs));
+    CU(cudaEventRecord(w->jk_ev[1], cs));
+    w->ctx->launches += 2;
+    CU(cudaMemcpy2DAsync(vj, (size_t)ldo * 8, Jd, (size_t)nmo * 8, (size_t)nmo * 8, (size_t)nmo, cudaMemcpyDeviceToHost, cs));
+    CU(cudaMemcpy2DAsync(vk, (size_t)ldo * 8, Kd, (size_t)nmo * 8, (size_t)nmo * 8, (size_t)nmo, cudaMemcpyDeviceToHost, cs));
+    w->ctx->d2h_bytes += 2 * nmo * nmo * 8;
+    CU(cudaStreamSynchronize(cs));
+    CU(cudaEventElapsedTime(&w->jk_ms, w->jk_ev[0], w->jk_ev[1]));
+    return QEMB_OK;
+}
+
+// device time of the last qemb_fragment_jk (both kernels) and its algorithmic bytes (8 npair^2: G read once)
+extern "C" int qemb_fragment_jk_time(const qemb_workspace *w, float *ms, double *bytes)
+{
+    REQ(w && ms, "null argument");
+    *ms = w->jk_ms;
+    if (bytes) {
+        const double np = (double)w->slot[w->cur].npair;
+        *bytes = 8.0 * np * np;
+    }
     return QEMB_OK;
 }
 

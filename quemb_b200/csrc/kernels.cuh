@@ -68,6 +68,23 @@ cudaError_t launch_invert_diag_blocks(const double *L, int64_t ldl, int nblocks,
 constexpr int TRSM_BLOCK = 128;
 constexpr int TRSM_PANEL = 64;
 
+// ---- J / K from the resident (ij|kl) (consumer of the path; jk.cu) -----------------------------------
+struct JkParams {
+    const double *G; // npair x npair, symmetric, s4 pair order
+    int64_t ldg;
+    int64_t npair;
+    int nmo;
+    const double *D;   // nmo x nmo symmetric density, column-major
+    const double *dpk; // packed weights: D[k,l] * (k == l ? 1 : 2) at T(k)+l
+    const int *crow;   // chunk table: packed rows [crow[c], crow[c+1]) form chunk c
+    int nchunks;
+    double *Jp;        // npair
+    double *R1, *R2;   // npair x nmo (row r at r*nmo)
+};
+cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int num_sms, cudaStream_t s);
+int jk_max_nmo();
+int jk_chunk_doubles();
+
 // ---- screening -------------------------------------------------------------------------------------
 // mask[mu + nao*i] = |sum_nu S[mu,nu] TA[nu,i]| >= eps  (left-to-right, no FMA contraction)
 cudaError_t launch_screen(const double *S, int64_t lds, const double *TA, int64_t ldta, int nao, int nmo,

@@ -158,6 +158,29 @@ class Workspace:
         keys = ["F_K1", "F_K2a", "F_K2b", "F_K3", "B_K1", "B_K2a", "B_K2b", "B_K3"]
         return dict(zip(keys, out.tolist()))
 
+    def jk(self, dm: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+        """``scf.hf.dot_eri_dm(eri, dm, hermi=1)`` on the (ij|kl) the last transform left on the device:
+        ``vj[i,j] = sum_kl (ij|kl) dm[k,l]``, ``vk[i,k] = sum_jl (ij|kl) dm[j,l]`` (``qemb_fragment_jk``)."""
+        D = _f64(dm, "dm")
+        if D.shape[0] != D.shape[1]:
+            raise _lib.QembError("dm must be square")
+        n = D.shape[0]
+        vj, vk = np.empty((n, n), order="F"), np.empty((n, n), order="F")
+        check(lib().qemb_fragment_jk(self._h, ptr(D), c_i64(_ld(D)), ptr(vj), ptr(vk), c_i64(n)))
+        return vj, vk
+
+    def jk_time(self) -> tuple[float, float]:
+        """(device ms, algorithmic bytes) of the last :meth:`jk`."""
+        ms, b = ctypes.c_float(), c_dbl()
+        check(lib().qemb_fragment_jk_time(self._h, ctypes.byref(ms), ctypes.byref(b)))
+        return float(ms.value), float(b.value)
+
+    def G(self, npair: int) -> np.ndarray:
+        """Download the resident (ij|kl) of the last transform."""
+        out = np.empty((npair, npair), order="F")
+        check(lib().qemb_fragment_get_G(self._h, ptr(out), c_i64(npair)))
+        return out
+
     def lists(self, nmo: int) -> list[list[int]]:
         aptr = np.zeros(nmo + 1, dtype=np.int64)
         check(lib().qemb_fragment_get_lists(self._h, ptr(aptr), None))
@@ -623,6 +646,22 @@ def transform_integral_device(
         ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
         c_i64(TA.shape[1]), c_dbl(MO_coeff_epsilon), c_i64(p_range[0]), c_i64(p_range[1]), c_p(out_dev_ptr),
         c_i64(ld_out), c_int(1), None))
+
+
+def transform_integral_resident(int_P_mu_nu: SemiSparseSym3DTensor, TA, S_abs, L_PQ, MO_coeff_epsilon: float, *,
+                                ws: Workspace | None = None) -> Workspace:
+    """Same path, (ij|kl) stays in the workspace (nothing travels to the host): the entry point of the
+    fused consumers (``Workspace.jk``; ``quemb_b200.consumer``).  Returns the workspace that holds G."""
+    ctx = int_P_mu_nu.ctx
+    ws = ws or default_workspace(ctx)
+    TA = _f64(TA, "TA")
+    int_P_mu_nu._flush()
+    sc = _screen_for(S_abs, ctx)
+    m = None if (L_PQ is None) else _metric_for(L_PQ, ctx)
+    check(lib().qemb_fragment_transform(
+        ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
+        c_i64(TA.shape[1]), c_dbl(MO_coeff_epsilon), c_i64(0), c_i64(-1), None, c_i64(0), c_int(0), None))
+    return ws
 
 
 def transform_integral_cuda(int_P_mu_nu, TA, S_abs, L_PQ: GPU_MatrixHandle, MO_coeff_epsilon: float) -> np.ndarray:

@@ -230,6 +230,8 @@ def make_lattice_problem(
     MO_coeff_epsilon: float = 1e-5,
     AO_coeff_epsilon: float = 1e-10,
     name: str = "lattice",
+    matmul=None,
+    n_sites: int | None = None,
 ) -> Problem:
     """Water-cluster-like 3-D lattice; a fragment = one site + its nearest sites."""
     rng = np.random.default_rng(seed)
@@ -238,13 +240,13 @@ def make_lattice_problem(
     S_abs = gaussian_S_abs(r, sigma)
     exch = get_AO_per_AO(S_abs, AO_coeff_epsilon)
     L = metric_cholesky(naux, cond, rng)
-    M = make_P_mu_nu(r, sigma, exch, L, rng)
+    M = make_P_mu_nu(r, sigma, exch, L, rng, matmul=matmul)
     site_of_ao = np.repeat(np.arange(n_side**3), ao_per_site)
     site_r = r[::ao_per_site]
     TAs = []
     for c in range(n_frag):
         d = np.sqrt(((site_r - site_r[c]) ** 2).sum(-1))
-        sites = np.nonzero(d < 1.3)[0]
+        sites = np.nonzero(d < 1.3)[0] if n_sites is None else np.sort(np.argsort(d, kind="stable")[:n_sites])
         frag_aos = np.nonzero(np.isin(site_of_ao, sites))[0]
         nb = len(frag_aos) if n_bath is None else min(n_bath, len(frag_aos))
         TAs.append(fragment_TA(r, frag_aos, nb, lam, rng))

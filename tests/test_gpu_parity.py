@@ -266,3 +266,107 @@ def test_aux_sharded_build_two_gpus(q, tmp_path):
         capture_output=True, text=True, timeout=600, env=dict(os.environ, PYTHONPATH=str(root)))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "SHARDED_OK" in r.stdout
+
+
+def test_octane_full_size_vs_compiled_reference(q):
+    """BASELINE.json configs[1] at full size (nao 202, naux 700, BE3-like fragments): the B200 path against the
+    reference's own compiled extension (oracle/_ref, built by oracle/Makefile) -- screening pattern bit-exact,
+    (ij|kl) <= 1e-10 -- for the smallest and the largest fragment, per-fragment solve and whitened tensor."""
+    ref = oracle.reference_module()
+    if ref is None:
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    p = syn.octane_like()
+    T_ref = ref.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), [x.tolist() for x in p.exch_reachable])
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    Tw = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    L = q.GPU_MatrixHandle(p.L_PQ)
+    Tw.whiten(L)
+    nmos = [t.shape[1] for t in p.TAs]
+    for f in (int(np.argmin(nmos)), int(np.argmax(nmos))):
+        TA = p.TAs[f]
+        assert q.get_AO_per_MO(TA, p.S_abs, p.MO_coeff_epsilon) == [list(a) for a in ref.get_AO_per_MO(TA, p.S_abs, p.MO_coeff_epsilon)]
+        G_ref = ref.transform_integral(T_ref, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+        G = q.transform_integral(T, TA, p.S_abs, L, p.MO_coeff_epsilon)
+        assert G.shape == G_ref.shape
+        assert np.abs(G - G_ref).max() <= TOL
+        Gw = q.transform_integral(Tw, TA, p.S_abs, None, p.MO_coeff_epsilon)
+        assert np.abs(Gw - G_ref).max() <= TOL
+
+
+@pytest.mark.parametrize("name", ["chain_small", "lattice_small"])
+def test_jk_consumer_on_resident_eri(q, name):
+    """Fused consumer: J/K and the HF-in-HF two-electron sum from the device-resident (ij|kl)
+    against the CPU restatements applied to the REFERENCE's golden G."""
+    from oracle import consumer_oracle as co
+    from quemb_b200 import consumer
+
+    g = Golden(name)
+    T = _tensor(q, g)
+    L = q.GPU_MatrixHandle(g.L)
+    rng = np.random.default_rng(11)
+    for f in range(g.n_frag):
+        fr = g.frag(f)
+        nmo = fr["TA"].shape[1]
+        ws = q.transform_integral_resident(T, fr["TA"], g.S_abs, L, g.eps)
+        npair = nmo * (nmo + 1) // 2
+        assert np.abs(ws.G(npair) - fr["G"]).max() <= TOL
+        C = np.linalg.qr(rng.standard_normal((nmo, nmo)))[0][:, : max(1, nmo // 3)]
+        D = 2.0 * C @ C.T
+        vj, vk = consumer.dot_eri_dm(ws, D)
+        vj_ref, vk_ref = co.dot_eri_dm(fr["G"], D)
+        assert np.abs(vj - vj_ref).max() <= 1e-10 and np.abs(vk - vk_ref).max() <= 1e-10
+        vj2, vk2 = consumer.dot_eri_dm(ws, D)
+        assert np.array_equal(vj, vj2) and np.array_equal(vk, vk2)  # deterministic (no atomics)
+        n_frag = max(1, nmo // 2)
+        e2 = consumer.ebe_hf_two_electron(ws, 0.5 * D, n_frag)
+        assert np.abs(e2 - co.ebe_hf_e2(fr["G"], 0.5 * D, n_frag)).max() <= 1e-10
+        # get_veff (helper.py:28-69) with an AO density / overlap / mean-field potential of matching shapes
+        S = np.eye(g.nao) + 0.01 * g.S_abs
+        dm = S @ fr["TA"] @ D @ fr["TA"].T @ S
+        hf_veff = 0.5 * (g.S_abs + g.S_abs.T)
+        Veff, Veff0 = consumer.get_veff(ws, dm, S, fr["TA"], hf_veff)
+        ST = S @ fr["TA"]
+        P_ = ST.T @ dm @ ST
+        vj_r, vk_r = co.dot_eri_dm(fr["G"], 0.5 * (P_ + P_.T))
+        assert np.abs(Veff - (fr["TA"].T @ hf_veff @ fr["TA"] - (vj_r - 0.5 * vk_r))).max() <= 1e-9 * max(1.0, np.abs(vj_r).max())
+    with pytest.raises(RuntimeError):
+        ws.jk(np.triu(np.ones((nmo, nmo))))  # not symmetric
+
+
+def test_jk_multi_chunk_matches_torch(q):
+    """nmo large enough for several shared-memory chunks per column (npair > 12288): J/K against a torch FP64
+    evaluation from the library's own resident G."""
+    import torch
+
+    p = syn.make_chain_problem(n_units=14, ao_per_unit=24, n_end=5, naux=300, frag_halfwidth=2, n_bath=60,
+                               sigma=0.94, seed=109, n_frag=8)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    T.whiten(p.L_PQ)
+    TA = p.TAs[6]
+    nmo = TA.shape[1]
+    npair = nmo * (nmo + 1) // 2
+    assert npair > 12288
+    ws = q.transform_integral_resident(T, TA, p.S_abs, None, p.MO_coeff_epsilon)
+    rng = np.random.default_rng(5)
+    D = rng.standard_normal((nmo, nmo))
+    D = D + D.T
+    vj, vk = ws.jk(D)
+    ms, nbytes = ws.jk_time()
+    assert ms > 0 and nbytes == 8.0 * npair * npair
+    Gt = torch.from_numpy(ws.G(npair)).cuda()
+    hi, lo = np.tril_indices(nmo)
+    idx = np.zeros((nmo, nmo), dtype=np.int64)
+    idx[hi, lo] = np.arange(npair)
+    idx[lo, hi] = np.arange(npair)
+    it = torch.from_numpy(idx).cuda()
+    Dt = torch.from_numpy(D).cuda()
+    # J: packed weights; K: row-block evaluation to bound memory
+    w = torch.where(torch.from_numpy(hi == lo).cuda(), 1.0, 2.0) * Dt[torch.from_numpy(hi).cuda(), torch.from_numpy(lo).cuda()]
+    vj_ref = (Gt @ w)[it].cpu().numpy()
+    assert np.abs(vj - vj_ref).max() <= 1e-10 * max(1.0, np.abs(vj_ref).max())
+    vk_ref = np.zeros((nmo, nmo))
+    for i in range(0, nmo, 16):  # K[i,k] = sum_jl G[idx[i,j], idx[k,l]] D[j,l]
+        rows = it[i:i + 16].reshape(-1)                                   # (16*nmo)
+        blk = Gt[rows][:, it.reshape(-1)].reshape(-1, nmo, nmo, nmo)      # [i, j, k, l]
+        vk_ref[i:i + 16] = torch.einsum("ijkl,jl->ik", blk, Dt).cpu().numpy()
+    assert np.abs(vk - vk_ref).max() <= 1e-10 * max(1.0, np.abs(vk_ref).max())

@@ -113,3 +113,22 @@ def test_live_reference_if_present():
         G = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ,
                                       p.MO_coeff_epsilon)
         assert np.abs(G - Gref).max() <= TOL
+
+
+def test_consumer_oracle_identity():
+    """The two restatements in oracle/consumer_oracle.py agree with each other through
+    e2[i] = sum_j D_ij (2J - K)_ij (the identity quemb_b200.consumer relies on), on a reference-produced G."""
+    from oracle import consumer_oracle as co
+
+    g = Golden("chain_small")
+    fr = g.frag(0)
+    G = fr["G"]
+    nmo = fr["TA"].shape[1]
+    rng = np.random.default_rng(3)
+    C = np.linalg.qr(rng.standard_normal((nmo, nmo)))[0][:, : max(1, nmo // 3)]
+    D = C @ C.T
+    vj, vk = co.dot_eri_dm(G, D)
+    assert np.allclose(vj, vj.T, atol=1e-13) and np.allclose(vk, vk.T, atol=1e-13)
+    n_frag = max(1, nmo // 2)
+    e2 = co.ebe_hf_e2(G, D, n_frag)
+    assert np.abs(e2 - np.einsum("ij,ij->i", D[:n_frag], 2 * vj[:n_frag] - vk[:n_frag])).max() <= 1e-12
