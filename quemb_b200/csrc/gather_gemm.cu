@@ -212,7 +212,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
     const int wm0 = (warp & 3) * WM, wni = warp >> 2;
     const int g = lane >> 2, t = lane & 3;
 
-    int s = 0, phase = 0;
+    // the "empty" arrive of a stage is deferred until after the wait for the next one (see k3_gram.cu: an arrive
+    // right behind the stage body is scheduled ahead of the DMMAs, i.e. before the stage's LDS are known to be done)
+    int s = 0, phase = 0, held = -1;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
         const int4 tt = p.tiles[tile];
         const GatherGroup grp = p.groups[tt.x];
@@ -226,6 +228,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
         acc.zero();
         for (int kt = 0; kt < ktiles; ++kt) {
             mbar_wait(&full[s], phase);
+            if (held >= 0) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[held]);
+            }
+            held = s;
             const double *As = reinterpret_cast<const double *>(smem + s * STAGE_BYTES);
             const double *Bs = reinterpret_cast<const double *>(smem + s * STAGE_BYTES + A_BYTES);
             switch (jv) {
@@ -234,8 +241,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) gather_gemm_kernel(GatherParams p
 #undef GG_CASE
             default: break;
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
             if (++s == STAGES) {
                 s = 0;
                 phase ^= 1;

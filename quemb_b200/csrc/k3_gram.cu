@@ -140,7 +140,13 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
 #pragma unroll
     for (int ks = 0; ks < BK / 4; ++ks) koff[ks] = (((4 * (t >> 1) + ks) ^ g) << 1) + (t & 1);
 
-    int s = 0, phase = 0;
+    // Stage release is DEFERRED by one stage: the "empty" arrive of stage s-1 is issued after the wait for stage s.
+    // ptxas schedules an arrive that directly follows the stage body right behind the last LDS *issue*, ahead of
+    // the DMMAs that consume them (seen in the SASS), i.e. before those loads are known to have completed; rows
+    // of the refill (TMA, async proxy) then sporadically reached a slow LDS: one 128-byte row of one warp wrong
+    // in ~1 of 10^4 tiles.  Behind the wait loop of the next stage every DMMA of stage s-1 has been issued, which
+    // needs its LDS operands in registers, so the release is safe by construction and costs no stall.
+    int s = 0, phase = 0, held = -1;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
         const int2 tt = p.tiles[tile];
         const int64_t m0 = (int64_t)tt.x * TM, n0 = (int64_t)tt.y * TN;
@@ -148,6 +154,11 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
         acc.zero();
         for (int kt = 0; kt < p.ktiles; ++kt) {
             mbar_wait(&full[s], phase);
+            if (held >= 0) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[held]);
+            }
+            held = s;
             const double *As = reinterpret_cast<const double *>(smem + s * STAGE_BYTES);
             const double *Bs = As + TILE_BYTES / 8;
 #pragma unroll
@@ -162,8 +173,6 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
 #pragma unroll
                     for (int j = 0; j < WN / 8; ++j) dmma884(acc.c[i][j][0], acc.c[i][j][1], a[i], b[j]);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
             if (++s == STAGES) {
                 s = 0;
                 phase ^= 1;

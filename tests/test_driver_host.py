@@ -183,3 +183,22 @@ def test_world_size_2_gloo_aux_sharded_reduce(tmp_path):
     assert r0["owned"] == list(range(0, res["nfrag"], 2)) and r1["owned"] == list(range(1, res["nfrag"], 2))
     errs = {**r0["errs"], **r1["errs"]}
     assert len(errs) == res["nfrag"] and max(errs.values()) <= 1e-10, errs
+
+
+def test_eri_file_container_roundtrip(tmp_path):
+    """Same dataset names / shape / dtype contract as the reference's HDF5 file (eri_sparse_DF.py:631)."""
+    from quemb_b200.eri_file import NpyDirFile, open_eri_file
+
+    rng = np.random.default_rng(0)
+    G = rng.standard_normal((21, 21))
+    G = G + G.T
+    with open_eri_file(tmp_path / "eri_file.h5", "w") as f:
+        f.create_dataset("f0", data=G)
+        f.create_dataset("f1", data=np.asfortranarray(2 * G))
+    with open_eri_file(tmp_path / "eri_file.h5", "r") as f:
+        assert np.array_equal(np.array(f.get("f0")), G) and np.array_equal(np.array(f["f1"]), 2 * G)
+        assert np.array(f.get("f0")).dtype == np.float64 and np.array(f.get("f0")).shape == (21, 21)
+        if isinstance(f, NpyDirFile):
+            assert f.get("f7") is None and f.keys() == ["f0", "f1"]
+            with pytest.raises(OSError):
+                f.create_dataset("f2", data=G)

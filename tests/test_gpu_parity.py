@@ -370,3 +370,56 @@ def test_jk_multi_chunk_matches_torch(q):
         blk = Gt[rows][:, it.reshape(-1)].reshape(-1, nmo, nmo, nmo)      # [i, j, k, l]
         vk_ref[i:i + 16] = torch.einsum("ijkl,jl->ik", blk, Dt).cpu().numpy()
     assert np.abs(vk - vk_ref).max() <= 1e-10 * max(1.0, np.abs(vk_ref).max())
+
+
+def test_dense_int_direct_DF_on_the_same_kernels(q):
+    """the unscreened limit against a numpy restatement of integral_direct_DF
+    (eri_onthefly.py:127-145)."""
+    import scipy.linalg as sla
+
+    from quemb_b200 import dense_df
+
+    rng = np.random.default_rng(21)
+    naux, nao, nmo = 90, 23, 9
+    pqL = rng.standard_normal((naux, nao, nao)) / np.sqrt(naux)
+    pqL = pqL + pqL.transpose(0, 2, 1)
+    low = syn.metric_cholesky(naux, 1e4, rng)
+    TA = np.linalg.qr(rng.standard_normal((nao, nmo)))[0]
+    got = {}
+    dense_df.integral_direct_DF(pqL, low, [TA], lambda i, G: got.__setitem__(i, G.copy()))
+    Lij = np.einsum("Lpq,pi,qj->Lij", pqL, TA, TA).reshape(naux, -1)
+    bb = sla.solve_triangular(low, Lij, lower=True)
+    eri_nosym = (bb.T @ bb).reshape(nmo, nmo, nmo, nmo)
+    hi, lo = np.tril_indices(nmo)
+    eri4 = eri_nosym[hi, lo][:, hi, lo]  # restore("4", ...): pair index T(max)+min
+    assert got[0].shape == eri4.shape
+    assert np.abs(got[0] - eri4).max() <= TOL
+
+
+def test_pipeline_stress_repeated_runs(q):
+    """Regression for the premature mbarrier stage release (round 1): K3 on the same X many times must equal a
+    cuBLAS FP64 X^T X entry by entry every time (the race hit ~1 row of 1 warp in 1 of 10^4 tiles, i.e. most runs
+    at this size), and K1/K2a must be bitwise reproducible."""
+    import torch
+
+    p = syn.octane_like()
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    L = q.GPU_MatrixHandle(p.L_PQ)
+    TA = p.TAs[3]
+    nmo = TA.shape[1]
+    npair = nmo * (nmo + 1) // 2
+    A = q.get_AO_per_MO(TA, p.S_abs, p.MO_coeff_epsilon)
+    B0 = S0 = Gt = None
+    for rep in range(12):
+        B = q.contract_with_TA_1st(TA, T, A)
+        Bd = B.dense_data
+        Sd = q.contract_with_TA_2nd_to_sym_dense(B, TA)
+        if B0 is None:
+            B0, S0 = Bd, Sd
+        assert np.array_equal(Bd, B0) and np.array_equal(Sd, S0)
+        ws = q.transform_integral_resident(T, TA, p.S_abs, L, p.MO_coeff_epsilon)
+        if Gt is None:
+            X = np.linalg.solve(np.tril(p.L_PQ), S0)
+            Xt = torch.from_numpy(np.ascontiguousarray(X)).cuda()
+            Gt = (Xt.T @ Xt).cpu().numpy()
+        assert np.abs(ws.G(npair) - Gt).max() <= TOL, f"repetition {rep}"
