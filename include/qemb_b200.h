@@ -81,6 +81,10 @@ int qemb_tensor_reachable_columns(const qemb_tensor *, int64_t *col /* nnz(exch)
 /* fills columns [col0, col0+ncols) from host (replaces writes through mut_unique_dense_data,
  * cpp:810-812, py:486-488) */
 int qemb_tensor_upload(qemb_tensor *, const double *host, int64_t ld_host, int64_t col0, int64_t ncols);
+/* Staging of one libcint block (replaces the Python triple loop py:459-488):
+ * block[(i * n_j + j) * naux + P] = (P | p0+i, q0+j), C order as `_aux_e2(...)` returns it; every screened pair
+ * with q0+j <= p0+i receives its column on the device, all other entries of the block are ignored. */
+int qemb_tensor_scatter_block(qemb_tensor *, const double *block, int64_t n_i, int64_t n_j, int64_t p0, int64_t q0);
 /* reads columns back (unique_dense_data / __getitem__, cpp:203-215, 806-826) */
 int qemb_tensor_download(const qemb_tensor *, double *host, int64_t ld_host, int64_t col0, int64_t ncols);
 
@@ -123,6 +127,9 @@ int qemb_workspace_bytes(const qemb_workspace *, int64_t *bytes);
  * ("the plan") and returns the total count.  TA is nao x nmo column-major on the host. */
 int qemb_fragment_screen(qemb_workspace *, const qemb_screen *, const double *TA_host, int64_t ld,
                          int64_t nao, int64_t nmo, double eps, int64_t *n_mu_i);
+/* number of (mu, i) of the last qemb_fragment_screen with | |X(mu,i)| - eps | < 1e-12: entries whose membership may
+ * differ from a producer that sums in another order (the reference is compiled -ffast-math) */
+int qemb_fragment_borderline(const qemb_workspace *, int64_t *n);
 /* plan from caller-supplied lists (the AO_by_MO argument of contract_with_TA_1st, pyi:126) */
 int qemb_fragment_set_lists(qemb_workspace *, const double *TA_host, int64_t ld, int64_t nao,
                             int64_t nmo, const int64_t *A_ptr, const int64_t *A_idx);

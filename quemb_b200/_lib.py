@@ -74,6 +74,7 @@ _SIGS = {
     "qemb_tensor_column": (c_int, [c_p, c_i64, c_i64, ctypes.POINTER(c_i64)]),
     "qemb_tensor_reachable_columns": (c_int, [c_p, c_p]),
     "qemb_tensor_upload": (c_int, [c_p, c_p, c_i64, c_i64, c_i64]),
+    "qemb_tensor_scatter_block": (c_int, [c_p, c_p, c_i64, c_i64, c_i64, c_i64]),
     "qemb_tensor_download": (c_int, [c_p, c_p, c_i64, c_i64, c_i64]),
     "qemb_metric_create": (c_int, [c_p, c_p, c_i64, c_i64, ctypes.POINTER(c_p)]),
     "qemb_metric_destroy": (None, [c_p]),
@@ -85,6 +86,7 @@ _SIGS = {
     "qemb_workspace_destroy": (None, [c_p]),
     "qemb_workspace_bytes": (c_int, [c_p, ctypes.POINTER(c_i64)]),
     "qemb_fragment_screen": (c_int, [c_p, c_p, c_p, c_i64, c_i64, c_i64, c_dbl, ctypes.POINTER(c_i64)]),
+    "qemb_fragment_borderline": (c_int, [c_p, ctypes.POINTER(c_i64)]),
     "qemb_fragment_set_lists": (c_int, [c_p, c_p, c_i64, c_i64, c_i64, c_p, c_p]),
     "qemb_fragment_get_lists": (c_int, [c_p, c_p, c_p]),
     "qemb_fragment_contract_1st": (c_int, [c_p, c_p]),

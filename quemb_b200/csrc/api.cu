@@ -251,6 +251,7 @@ struct PlanDev { // device pointers into a slot's plan buffer
 
 struct Slot {
     int64_t nao = 0, nmo = 0, npair = 0, nA = 0;
+    int64_t n_borderline = 0; // screened entries within 1e-12 of the threshold (last qemb_fragment_screen)
     std::vector<int64_t> aptr, aidx;
     DevBuf TA, mask, plan1, plan2;
     HostBuf stage1, stage2, hmask;
@@ -313,6 +314,7 @@ struct qemb_workspace {
     double *G_last = nullptr; // where the last K3 wrote
     int64_t G_last_ld = 0;
     bool have_G = false;
+    DevBuf gram_partial; // split-K partial tiles of K3 for small fragments
     // J/K consumer (jk.cu)
     DevBuf jk_in, jk_scratch, jk_out;
     cudaEvent_t jk_ev[2] = {nullptr, nullptr};
@@ -694,6 +696,46 @@ extern "C" int qemb_tensor_upload(qemb_tensor *t, const double *host, int64_t ld
     return QEMB_OK;
 }
 
+// (mu nu|P) staging without the Python triple loop (py:459-488): one libcint block `integrals[i, j, P]` (C order,
+// P contiguous) for the AOs mu = p0 + i, nu = q0 + j is uploaded once and scattered on the device into the columns
+// of the screened pairs with nu <= mu (pairs outside the screened set are skipped, like the key_to_offset test).
+extern "C" int qemb_tensor_scatter_block(qemb_tensor *t, const double *block, int64_t n_i, int64_t n_j, int64_t p0,
+                                         int64_t q0)
+{
+    REQ(t && (block || n_i * n_j == 0), "null argument");
+    REQ(n_i >= 0 && n_j >= 0 && p0 >= 0 && q0 >= 0 && p0 + n_i <= t->nao && q0 + n_j <= t->nao, "AO block outside the tensor");
+    const int64_t npairs = n_i * n_j;
+    if (npairs == 0) return QEMB_OK;
+    REQ(npairs < std::numeric_limits<int32_t>::max(), "block too large");
+    std::vector<int32_t> col((size_t)npairs, -1);
+    int64_t live = 0;
+    for (int64_t i = 0; i < n_i; ++i)
+        for (int64_t j = 0; j < n_j; ++j) {
+            const int64_t mu = p0 + i, nu = q0 + j;
+            if (nu > mu) break; // "still ensure p <= q" of the reference loop (py:476-480)
+            const int64_t c = find_column(t->uptr, t->uidx, mu, nu);
+            if (c >= 0) {
+                col[(size_t)(i * n_j + j)] = (int32_t)c;
+                ++live;
+            }
+        }
+    if (live == 0) return QEMB_OK;
+    DeviceGuard g(t->ctx->device);
+    cudaStream_t s = t->ctx->compute;
+    const size_t bbytes = (size_t)npairs * (size_t)t->naux * 8, cbytes = (size_t)npairs * 4;
+    const size_t coff = (bbytes + 15) & ~size_t(15);
+    TRY(t->scratch.reserve(coff + cbytes));
+    char *d = static_cast<char *>(t->scratch.p);
+    TRY(upload_2d(t->ctx, d, bbytes, block, bbytes, bbytes, 1, s));
+    CU(cudaMemcpyAsync(d + coff, col.data(), cbytes, cudaMemcpyHostToDevice, s));
+    CU(launch_scatter_block(reinterpret_cast<const double *>(d), reinterpret_cast<const int *>(d + coff), (int)npairs,
+                            (int)t->naux, t->data.as<double>(), t->ldp, s));
+    t->ctx->launches += 1;
+    CU(cudaStreamSynchronize(s)); // col (host vector) and the caller's block may be reused
+    t->whitened = false;
+    return QEMB_OK;
+}
+
 extern "C" int qemb_tensor_download(const qemb_tensor *t, double *host, int64_t ld_host, int64_t col0, int64_t ncols)
 {
     REQ(t && (host || ncols == 0), "null argument");
@@ -933,6 +975,7 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     for (auto &e : w->jk_ev)
         if (e) cudaEventDestroy(e);
     w->jk_in.release();
+    w->gram_partial.release();
     w->jk_scratch.release();
     w->jk_out.release();
     w->Bint.release();
@@ -1227,15 +1270,25 @@ extern "C" int qemb_fragment_screen(qemb_workspace *w, const qemb_screen *sc, co
     const uint8_t *m = static_cast<const uint8_t *>(s.hmask.p);
     s.aptr.assign(nmo + 1, 0);
     s.aidx.clear();
+    s.n_borderline = 0;
     for (int64_t i = 0; i < nmo; ++i) {
         const uint8_t *col = m + i * nao;
-        for (int64_t mu = 0; mu < nao; ++mu)
-            if (col[mu]) s.aidx.push_back(mu);
+        for (int64_t mu = 0; mu < nao; ++mu) {
+            if (col[mu] & 1) s.aidx.push_back(mu);
+            if (col[mu] & 2) ++s.n_borderline;
+        }
         s.aptr[i + 1] = (int64_t)s.aidx.size();
     }
     s.nA = (int64_t)s.aidx.size();
     REQ(s.nA < std::numeric_limits<int32_t>::max(), "AO_by_MO too large");
     if (n_mu_i) *n_mu_i = s.nA;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_borderline(const qemb_workspace *w, int64_t *n)
+{
+    REQ(w && n && w->started, "no fragment planned");
+    *n = w->slot[w->cur].n_borderline;
     return QEMB_OK;
 }
 
@@ -1399,13 +1452,18 @@ int gram(qemb_workspace *w, double *dst, int64_t ld)
     p.npair = s.npair;
     p.G = dst;
     p.ldg = ld;
+    const int nsplit = gram_splits(p.ntiles, p.ktiles, w->ctx->num_sms);
+    if (nsplit > 1) { // small fragment: fewer tiles than SMs, split the auxiliary index (deterministic two-pass sum)
+        TRY(w->gram_partial.reserve((size_t)nsplit * (size_t)s.npair * (size_t)s.npair * 8));
+        p.partial = w->gram_partial.as<double>();
+    }
     cudaStream_t cs = w->ctx->compute;
     if (w->ctx->timing && !w->ev_valid[3]) { // no solve in between: K3 starts where K2a ended
         CU(cudaEventRecord(w->ev[3], cs));
         w->ev_valid[3] = true;
     }
     CU(launch_gram(p, w->ctx->num_sms, cs));
-    w->ctx->launches += 1;
+    w->ctx->launches += nsplit > 1 ? 2 : 1;
     if (w->ctx->timing) {
         CU(cudaEventRecord(w->ev[4], cs));
         w->ev_valid[4] = true;
@@ -1676,7 +1734,8 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
         for (int64_t l = 0; l <= k; ++l) hin[oP / 8 + k * (k + 1) / 2 + l] = (k == l ? 1.0 : 2.0) * D[k + ldd * l];
     std::memcpy(reinterpret_cast<char *>(hin.data()) + oC, crow.data(), crow.size() * 4);
     TRY(w->jk_in.reserve(in_bytes));
-    TRY(w->jk_scratch.reserve(((size_t)npair + 2 * (size_t)npair * nmo) * 8));
+    const int64_t njp = npair * jk_warps();
+    TRY(w->jk_scratch.reserve(((size_t)njp + 2 * (size_t)npair * nmo) * 8));
     TRY(w->jk_out.reserve(2 * (size_t)nmo * nmo * 8));
     CU(cudaMemcpyAsync(w->jk_in.p, hin.data(), in_bytes, cudaMemcpyHostToDevice, cs));
     w->ctx->h2d_bytes += (int64_t)in_bytes;
@@ -1690,7 +1749,7 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     p.crow = reinterpret_cast<const int *>(static_cast<char *>(w->jk_in.p) + oC);
     p.nchunks = nch;
     p.Jp = w->jk_scratch.as<double>();
-    p.R1 = p.Jp + npair;
+    p.R1 = p.Jp + njp;
     p.R2 = p.R1 + npair * nmo;
     double *Jd = w->jk_out.as<double>(), *Kd = Jd + nmo * nmo;
     for (auto &e : w->jk_ev)

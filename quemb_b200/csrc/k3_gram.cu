@@ -86,6 +86,10 @@ struct GramTmaParams {
     int64_t ldg;
     const int2 *tiles;
     int ntiles;
+    // split-K for small npair (fewer tiles than SMs): work item w = (tile w / nsplit, k range of split w % nsplit),
+    // split s writes its partial tile into G + s * split_stride; gram_reduce_kernel adds them up in a fixed order
+    int nsplit, kchunk;
+    int64_t split_stride;
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -113,10 +117,11 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == NCONSUMER_WARPS && lane == 0) {
             int s = 0, phase = 0;
-            for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-                const int2 tt = p.tiles[tile];
+            for (int w = blockIdx.x; w < p.ntiles * p.nsplit; w += gridDim.x) {
+                const int2 tt = p.tiles[w / p.nsplit];
                 const int m0 = tt.x * TM, n0 = tt.y * TN;
-                for (int kt = 0; kt < p.ktiles; ++kt) {
+                const int kbeg = (w % p.nsplit) * p.kchunk, kend = min(p.ktiles, kbeg + p.kchunk);
+                for (int kt = kbeg; kt < kend; ++kt) {
                     mbar_wait(&empty[s], phase ^ 1);
                     mbar_expect_tx(&full[s], STAGE_BYTES);
                     uint8_t *As = smem + s * STAGE_BYTES;
@@ -147,12 +152,15 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
     // in ~1 of 10^4 tiles.  Behind the wait loop of the next stage every DMMA of stage s-1 has been issued, which
     // needs its LDS operands in registers, so the release is safe by construction and costs no stall.
     int s = 0, phase = 0, held = -1;
-    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        const int2 tt = p.tiles[tile];
+    for (int w = blockIdx.x; w < p.ntiles * p.nsplit; w += gridDim.x) {
+        const int2 tt = p.tiles[w / p.nsplit];
         const int64_t m0 = (int64_t)tt.x * TM, n0 = (int64_t)tt.y * TN;
+        const int split = w % p.nsplit;
+        const int kbeg = split * p.kchunk, kend = min(p.ktiles, kbeg + p.kchunk);
+        double *__restrict__ Gout = p.G + (int64_t)split * p.split_stride;
         WarpAcc<WM, WN> acc;
         acc.zero();
-        for (int kt = 0; kt < p.ktiles; ++kt) {
+        for (int kt = kbeg; kt < kend; ++kt) {
             mbar_wait(&full[s], phase);
             if (held >= 0) {
                 __syncwarp();
@@ -191,12 +199,25 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
                 for (int e = 0; e < 2; ++e) {
                     if (col + e < p.npair) {
                         const double v = acc.c[i][j][e];
-                        p.G[row + p.ldg * (col + e)] = v;
-                        if (offdiag) p.G[(col + e) + p.ldg * row] = v;
+                        Gout[row + p.ldg * (col + e)] = v;
+                        if (offdiag) Gout[(col + e) + p.ldg * row] = v;
                     }
                 }
             }
         }
+    }
+}
+
+// G[:, c] = sum_s P[s][:, c] in the fixed order s = 0 .. nsplit-1 (deterministic)
+__global__ void gram_reduce_kernel(const double *__restrict__ P, int64_t stride, int nsplit, int64_t npair,
+                                   double *__restrict__ G, int64_t ldg)
+{
+    const int64_t total = npair * npair;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        double v = 0.0;
+        for (int s2 = 0; s2 < nsplit; ++s2) v += P[(int64_t)s2 * stride + i];
+        const int64_t c = i / npair, r = i - c * npair;
+        G[r + ldg * c] = v;
     }
 }
 
@@ -219,6 +240,18 @@ EncodeTiledFn get_encode()
 }
 } // namespace
 
+// k splits worth using for `ntiles` output tiles: none once the tiles alone fill the SMs; otherwise enough work
+// items for ~2 per SM, each at least 4 k tiles deep
+int gram_splits(int ntiles, int ktiles, int num_sms)
+{
+    if (ntiles <= 0 || ntiles >= num_sms || ktiles < 8) return 1;
+    int want = (2 * num_sms + ntiles - 1) / ntiles;
+    want = want < ktiles / 4 ? want : ktiles / 4;
+    if (want <= 1) return 1;
+    const int kchunk = (ktiles + want - 1) / want;
+    return (ktiles + kchunk - 1) / kchunk;
+}
+
 cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
 {
     if (p.ntiles <= 0) return cudaSuccess;
@@ -235,9 +268,23 @@ cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles};
-    const int grid = p.ntiles < num_sms ? p.ntiles : num_sms;
+    const int nsplit = p.partial ? gram_splits(p.ntiles, p.ktiles, num_sms) : 1;
+    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles, 1, p.ktiles, 0};
+    if (nsplit > 1) {
+        kp.G = p.partial;
+        kp.ldg = p.npair;
+        kp.nsplit = nsplit;
+        kp.kchunk = (p.ktiles + nsplit - 1) / nsplit;
+        kp.split_stride = p.npair * p.npair;
+    }
+    const int nwork = p.ntiles * kp.nsplit;
+    const int grid = nwork < num_sms ? nwork : num_sms;
     gram_kernel<<<grid, NTHREADS, SMEM_BYTES, s>>>(tmap, kp);
+    e = cudaGetLastError();
+    if (e != cudaSuccess || nsplit == 1) return e;
+    const int64_t blocks = (p.npair * p.npair + 255) / 256;
+    gram_reduce_kernel<<<(unsigned)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, s>>>(p.partial, kp.split_stride, nsplit,
+                                                                                    p.npair, p.G, p.ldg);
     return cudaGetLastError();
 }
 

@@ -15,7 +15,10 @@ struct GramParams {
     int64_t ldg;
     const int2 *tiles; // (ti, tj), ti >= tj, L2-friendly order
     int ntiles;
+    double *partial = nullptr; // split-K scratch: gram_splits(...) x npair^2 doubles, or null (no split)
 };
+// number of k splits launch_gram uses when `partial` is given (1 = no split, no scratch needed)
+int gram_splits(int ntiles, int ktiles, int num_sms);
 // TMA + mbarrier pipeline, persistent (one CTA per SM, grid = min(ntiles, num_sms))
 cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s);
 // host: fills the lower-triangular tile list for nt row tiles; returns count
@@ -78,12 +81,13 @@ struct JkParams {
     const double *dpk; // packed weights: D[k,l] * (k == l ? 1 : 2) at T(k)+l
     const int *crow;   // chunk table: packed rows [crow[c], crow[c+1]) form chunk c
     int nchunks;
-    double *Jp;        // npair
+    double *Jp;        // npair x jk_warps() per-warp partial sums of J
     double *R1, *R2;   // npair x nmo (row r at r*nmo)
 };
 cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int num_sms, cudaStream_t s);
 int jk_max_nmo();
 int jk_chunk_doubles();
+int jk_warps();
 
 // ---- screening -------------------------------------------------------------------------------------
 // mask[mu + nao*i] = |sum_nu S[mu,nu] TA[nu,i]| >= eps  (left-to-right, no FMA contraction)
@@ -95,6 +99,8 @@ cudaError_t launch_fill(double *p, int64_t n, double v, cudaStream_t s);
 // zero rows [r0, r1) of every column of a column-major matrix
 cudaError_t launch_zero_rows(double *p, int64_t ld, int64_t r0, int64_t r1, int64_t ncol, cudaStream_t s);
 
+cudaError_t launch_scatter_block(const double *block, const int *col, int npairs, int naux, double *M, int64_t ld,
+                                 cudaStream_t s);
 cudaError_t launch_set_diag(double *p, int64_t ld, int64_t i0, int64_t i1, double v, cudaStream_t s);
 
 } // namespace qemb

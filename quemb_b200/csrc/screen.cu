@@ -19,7 +19,9 @@ __global__ void __launch_bounds__(128) screen_kernel(const double *__restrict__ 
     const double *ta = TA + (int64_t)i * ldta;
     double s = 0.0;
     for (int nu = 0; nu < nao; ++nu) s = __dadd_rn(s, __dmul_rn(S[mu + (int64_t)nu * lds], ta[nu]));
-    mask[mu + (int64_t)nao * i] = (fabs(s) >= eps) ? 1 : 0;
+    // bit 0: kept; bit 1: borderline -- within 1e-12 of the threshold, where another summation order
+    // (the reference is built with -ffast-math) may decide differently
+    mask[mu + (int64_t)nao * i] = ((fabs(s) >= eps) ? 1 : 0) | ((fabs(fabs(s) - eps) < 1e-12) ? 2 : 0);
 }
 
 cudaError_t launch_screen(const double *S, int64_t lds, const double *TA, int64_t ldta, int nao, int nmo,
@@ -58,6 +60,26 @@ cudaError_t launch_zero_rows(double *p, int64_t ld, int64_t r0, int64_t r1, int6
     if (nr <= 0 || ncol <= 0) return cudaSuccess;
     const int64_t blocks = (nr * ncol + 255) / 256;
     zero_rows_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, s>>>(p, ld, r0, nr, ncol);
+    return cudaGetLastError();
+}
+
+// (mu nu|P) staging: block[(i * n_j + j) * naux + P]  ->  M[P + ld * col[i * n_j + j]]  for col >= 0
+__global__ void scatter_block_kernel(const double *__restrict__ block, const int *__restrict__ col, int npairs,
+                                     int naux, double *__restrict__ M, int64_t ld)
+{
+    for (int pr = blockIdx.x; pr < npairs; pr += gridDim.x) {
+        const int c = col[pr];
+        if (c < 0) continue;
+        const double *src = block + (int64_t)pr * naux;
+        double *dst = M + (int64_t)c * ld;
+        for (int P = threadIdx.x; P < naux; P += blockDim.x) dst[P] = src[P];
+    }
+}
+cudaError_t launch_scatter_block(const double *block, const int *col, int npairs, int naux, double *M, int64_t ld,
+                                 cudaStream_t s)
+{
+    if (npairs <= 0 || naux <= 0) return cudaSuccess;
+    scatter_block_kernel<<<npairs < 148 * 8 ? npairs : 148 * 8, 256, 0, s>>>(block, col, npairs, naux, M, ld);
     return cudaGetLastError();
 }
 

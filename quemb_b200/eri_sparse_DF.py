@@ -181,6 +181,13 @@ class Workspace:
         check(lib().qemb_fragment_get_G(self._h, ptr(out), c_i64(npair)))
         return out
 
+    @property
+    def borderline(self) -> int:
+        """Entries of the last screening within 1e-12 of ``MO_coeff_epsilon``."""
+        n = c_i64()
+        check(lib().qemb_fragment_borderline(self._h, ctypes.byref(n)))
+        return n.value
+
     def lists(self, nmo: int) -> list[list[int]]:
         aptr = np.zeros(nmo + 1, dtype=np.int64)
         check(lib().qemb_fragment_get_lists(self._h, ptr(aptr), None))
@@ -335,6 +342,17 @@ class SemiSparseSym3DTensor:
         d = _f64(data, "data")
         check(lib().qemb_tensor_upload(self._h, ptr(d), c_i64(d.strides[1] // 8 if d.shape[1] > 1 else d.shape[0]),
                                        c_i64(col0), c_i64(d.shape[1])))
+
+    def scatter_block(self, integrals: np.ndarray, p0: int, q0: int) -> None:
+        """Device-side replacement of the Python scatter loop of ``get_sparse_P_mu_nu``
+        (``eri_sparse_DF.py:459-488``): ``integrals[i, j, :]`` (the C-ordered ``(n_i, n_j, naux)`` block
+        ``_aux_e2`` returns for the AOs ``p0 + i`` / ``q0 + j``) goes to the column of every screened pair with
+        ``q0 + j <= p0 + i``; one upload and one kernel per block instead of one numpy slice per pair."""
+        self._flush()
+        a = np.ascontiguousarray(integrals, dtype=np.float64)
+        if a.ndim != 3 or a.shape[2] != self._shape[0]:
+            raise _lib.QembError("integrals must have shape (n_i, n_j, naux)")
+        check(lib().qemb_tensor_scatter_block(self._h, ptr(a), c_i64(a.shape[0]), c_i64(a.shape[1]), c_i64(p0), c_i64(q0)))
 
     def _flush(self) -> None:
         if self._dirty and self._host_mirror is not None:

@@ -113,6 +113,16 @@ def main():
                           "gbs": wk[bk] / t / 1e9 if t > 0 else None}
                 tot_f += wk[fk]
                 tot_ms += best[k]
+            # J/K consumer on the resident matrix (HBM bound: 8 npair^2 bytes read once)
+            rng = np.random.default_rng(0)
+            D = rng.standard_normal((n, n))
+            D = D + D.T
+            jk_ms = None
+            for _ in range(2):
+                ws.jk(D)
+                ms_jk, nbytes = ws.jk_time()
+                jk_ms = ms_jk if jk_ms is None else min(jk_ms, ms_jk)
+            row["JK"] = {"ms": jk_ms, "gbs": nbytes / (jk_ms * 1e-3) / 1e9 if jk_ms else None}
             row["total_ms"] = tot_ms + best["screen"]
             row["total_tflops"] = tot_f / (row["total_ms"] * 1e-3) / 1e12
             rows.append(row)

@@ -423,3 +423,44 @@ def test_pipeline_stress_repeated_runs(q):
             Xt = torch.from_numpy(np.ascontiguousarray(X)).cuda()
             Gt = (Xt.T @ Xt).cpu().numpy()
         assert np.abs(ws.G(npair) - Gt).max() <= TOL, f"repetition {rep}"
+
+
+def test_borderline_screening_entries_are_reported(q):
+    """entries within 1e-12 of the threshold are counted instead of passing silently."""
+    nao, eps = 6, 1e-5
+    S = np.eye(nao)
+    TA = np.zeros((nao, 2), order="F")
+    TA[0, 0] = 1.0          # far above
+    TA[1, 0] = eps          # exactly on the threshold: kept (>=), borderline
+    TA[2, 0] = eps * (1 - 1e-9)  # 1e-14 below: dropped, borderline
+    TA[3, 0] = 0.5 * eps    # clearly dropped
+    TA[4, 1] = -eps * (1 + 1e-9)  # 1e-14 above in magnitude: kept, borderline
+    ws = q.default_workspace(q.default_context())
+    A = q.get_AO_per_MO(TA, S, eps, ws=ws)
+    assert A == [[0, 1], [4]]
+    assert ws.borderline == 3
+    assert A == [a.tolist() for a in oracle.get_AO_per_MO(TA, S, eps)]
+
+
+@pytest.mark.parametrize("name", ["chain_small", "asym_sources"])
+def test_block_staging_replaces_the_python_scatter_loop(q, name):
+    """(mu nu|P) arrives as libcint-style blocks integrals[i, j, P] per (shell, shell range) and is
+    scattered on the device; the tensor must equal, bit for bit, the one the reference's loop (py:459-488) fills."""
+    g = Golden(name)
+    T = q.SemiSparseSym3DTensor((g.naux, g.nao, g.nao), [x.tolist() for x in g.exch])
+    rng = np.random.default_rng(2)
+    shell = 3  # AOs per fake shell
+    for p0 in range(0, g.nao, shell):
+        n_i = min(shell, g.nao - p0)
+        for q0 in range(0, p0 + n_i, 2 * shell):  # ranges of two shells, like get_blocks' contiguous runs
+            n_j = min(2 * shell, g.nao - q0)
+            blk = rng.standard_normal((n_i, n_j, g.naux))  # unscreened / upper-triangle entries: must be ignored
+            for i in range(n_i):
+                for j in range(n_j):
+                    key = indexing.ravel_symmetric(p0 + i, q0 + j)
+                    if q0 + j <= p0 + i and key in g.offsets:
+                        blk[i, j, :] = g.M[:, g.offsets[key]]
+            T.scatter_block(blk, p0, q0)
+    np.testing.assert_array_equal(T.unique_dense_data, g.M)
+    fr = g.frag(0)
+    assert np.abs(q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps) - fr["G"]).max() <= TOL
