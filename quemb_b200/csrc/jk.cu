@@ -13,11 +13,14 @@
 // "row" ij of the s4 matrix is the contiguous column ij.  A CTA streams a column through shared memory in chunks
 // of whole packed rows k (cp.async double buffer) and unpacks it implicitly: with V[k,l] = (ij|kl),
 //     v_x[k] = sum_l V[k,l] x[l] = sum_{l<=k} P[T(k)+l] x[l]  +  sum_{m>k} P[T(m)+k] x[m]
-//   pass A (first sum):  a warp takes two packed rows, lanes over l, one transposed butterfly for the four sums
-//   pass B (second sum): thread per column l of the packed triangle, running over the rows k > l of the chunk;
-//                        consecutive threads read consecutive shared-memory words (conflict free)
-// for x = D[:,j] (-> contribution of row (i,j) to K[i,:]) and x = D[:,i] (-> K[j,:]), plus J[ij] in pass B (the
-// weights dpk are read coalesced, independent of the accumulators, so their latency overlaps).
+//   A role (first sum,  warps 0..7):  one THREAD per packed row k, running over l <= k.  T(k) mod 16 is a permutation
+//                         over any 16 consecutive k, so the 16 lanes of an LDS.64 phase hit 16 distinct banks; the
+//                         sums stay in the thread, no reduction
+//   B role (second sum, warps 8..15): one thread per column l of the packed triangle, running over the rows k > l of
+//                         the chunk; consecutive threads read consecutive words
+//   J[ij] = P . dpk:      element-wise over the chunk by all threads (coalesced weights, independent loads)
+// for x = D[:,j] (-> contribution of row (i,j) to K[i,:]) and x = D[:,i] (-> K[j,:]).  Both roles work on the same
+// chunk at the same time and have the same amount of work (the two halves of the symmetric matrix).
 // No atomics: per-column results go to R1/R2 (npair x nmo) and a second kernel sums them in a fixed order, so
 // the result is deterministic.
 #include "common.cuh"
@@ -33,63 +36,20 @@ constexpr int JK_NMO_MAX = 768;
 
 __device__ __forceinline__ int64_t tri(int64_t k) { return k * (k + 1) / 2; }
 
-// sums v0..v3 over the warp with one transposed butterfly (6 shuffles): afterwards lanes 0 / 8 / 16 / 24 (and the
-// lanes that share their bits 3,4) hold the totals of v0 / v1 / v2 / v3
-__device__ __forceinline__ double reduce4(double v0, double v1, double v2, double v3, int lane)
-{
-    const bool h16 = lane & 16, h8 = lane & 8;
-    double ka = h16 ? v2 : v0, kb = h16 ? v3 : v1;
-    ka += __shfl_xor_sync(0xffffffffu, h16 ? v0 : v2, 16);
-    kb += __shfl_xor_sync(0xffffffffu, h16 ? v1 : v3, 16);
-    double kk = h8 ? kb : ka;
-    kk += __shfl_xor_sync(0xffffffffu, h8 ? ka : kb, 8);
-    kk += __shfl_xor_sync(0xffffffffu, kk, 4);
-    kk += __shfl_xor_sync(0xffffffffu, kk, 2);
-    kk += __shfl_xor_sync(0xffffffffu, kk, 1);
-    return kk;
-}
 } // namespace
 
-// One packed row k of the column in shared memory, handled by one warp: lane owns the columns l = lane + 32 m.
-//   A term: a_i/a_j += P[T(k)+l] x[l]          (reduced over the lanes at the end of the row pair)
-//   B term: vb[m]   += P[T(k)+l] x[k],  l < k  (stays in the lane's registers for the whole column of G)
-//   J     : jw      += P[T(k)+l] dpk[T(k)+l]
-template <int MMAX>
-__device__ __forceinline__ void jk_row(const double *__restrict__ row, const double *__restrict__ dk, int k, int lane,
-                                       const double2 *__restrict__ x2, double (&vbi)[MMAX], double (&vbj)[MMAX],
-                                       double &ai, double &aj, double &jw)
+template <int QMAX>
+__global__ void __launch_bounds__(512, 1) jk_rows_kernel(JkParams p)
 {
-    const double2 xk = x2[k];
-#pragma unroll
-    for (int m = 0; m < MMAX; ++m) {
-        if (32 * m > k) break; // warp uniform
-        const int l = lane + 32 * m;
-        if (l <= k) {
-            const double g = row[l];
-            const double2 x = x2[l];
-            ai = fma(g, x.x, ai);
-            aj = fma(g, x.y, aj);
-            jw = fma(g, __ldg(dk + l), jw);
-            if (l < k) {
-                vbi[m] = fma(g, xk.x, vbi[m]);
-                vbj[m] = fma(g, xk.y, vbj[m]);
-            }
-        }
-    }
-}
-
-template <int MMAX, int NTHREADS>
-__global__ void __launch_bounds__(NTHREADS, 1) jk_rows_kernel(JkParams p)
-{
-    constexpr int NWARPS = NTHREADS / 32;
-    constexpr int NP = 32 * MMAX; // padded nmo of the cross-warp reduction
-    static_assert(NWARPS * NP <= JK_CHUNK, "cross-warp reduction must fit a chunk buffer");
+    constexpr int NTHREADS = 512, GA = 256, GB = 256; // A role: threads 0..255, B role: threads 256..511
     extern __shared__ __align__(16) double jk_smem[];
     double *buf0 = jk_smem, *buf1 = jk_smem + JK_BUF;
     double2 *x2 = reinterpret_cast<double2 *>(jk_smem + 2 * JK_BUF); // (D[l,i], D[l,j])
-    double2 *va2 = x2 + JK_NMO_MAX;                                  // A-term results per packed row
+    double2 *va2 = x2 + JK_NMO_MAX;                                  // A-role results per packed row
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool roleB = tid >= GA;
+    const int tb = tid - GA;
     const int nmo = p.nmo, nch = p.nchunks;
 
     // chunk c of column r: packed rows [crow[c], crow[c+1]); stored at dst + shift so that 16-byte copies line up
@@ -112,7 +72,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) jk_rows_kernel(JkParams p)
     prefetch(buf0, r, 0);
     cp_async_commit();
 
-    double vbi[MMAX], vbj[MMAX], jw = 0.0;
+    double bi[QMAX], bj[QMAX], jw = 0.0;
     while (r < p.npair) {
         if (c == 0) { // new column: (i, j) with i >= j, density columns, accumulators
             int i = (int)((sqrt(8.0 * (double)r + 1.0) - 1.0) * 0.5);
@@ -122,7 +82,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) jk_rows_kernel(JkParams p)
             for (int l = tid; l < nmo; l += NTHREADS)
                 x2[l] = make_double2(p.D[l + (int64_t)nmo * i], p.D[l + (int64_t)nmo * j]);
 #pragma unroll
-            for (int m = 0; m < MMAX; ++m) vbi[m] = vbj[m] = 0.0;
+            for (int q = 0; q < QMAX; ++q) bi[q] = bj[q] = 0.0;
             jw = 0.0;
         }
         int64_t rn = r;
@@ -142,45 +102,99 @@ __global__ void __launch_bounds__(NTHREADS, 1) jk_rows_kernel(JkParams p)
         __syncthreads(); // chunk landed; x2 visible
 
         const int k0 = p.crow[c], k1 = p.crow[c + 1];
-        const int64_t o0 = tri(k0);
+        const int o0 = (int)tri(k0);
         const double *cur = curbuf + ((reinterpret_cast<uintptr_t>(chunk_src(r, c)) >> 3) & 1);
-        // rows of the chunk, two per warp and step (k, k + NWARPS): one transposed reduction for the four A sums
-        for (int k = k0 + warp; k < k1; k += 2 * NWARPS) {
-            const int kb = k + NWARPS;
-            double a0i = 0.0, a0j = 0.0, a1i = 0.0, a1j = 0.0;
-            jk_row<MMAX>(cur + (tri(k) - o0), p.dpk + tri(k), k, lane, x2, vbi, vbj, a0i, a0j, jw);
-            if (kb < k1) jk_row<MMAX>(cur + (tri(kb) - o0), p.dpk + tri(kb), kb, lane, x2, vbi, vbj, a1i, a1j, jw);
-            const double t = reduce4(a0i, a0j, a1i, a1j, lane);
-            if ((lane & 7) == 0) {
-                const bool h16 = lane & 16, h8 = lane & 8;
-                if (!h16 || kb < k1) reinterpret_cast<double *>(va2 + (h16 ? kb : k))[h8 ? 1 : 0] = t;
+        // J += P . dpk over the chunk, element-wise by all threads: coalesced weights, independent loads (a weight
+        // load inside the B loop put an L2 latency on the critical path of every row)
+        {
+            const double *dk = p.dpk + o0;
+            const int ne = (int)tri(k1) - o0;
+            double j0 = 0.0, j1 = 0.0, j2 = 0.0, j3 = 0.0;
+            int e = tid;
+            for (; e + 3 * NTHREADS < ne; e += 4 * NTHREADS) {
+                const double w0 = __ldg(dk + e), w1 = __ldg(dk + e + NTHREADS), w2 = __ldg(dk + e + 2 * NTHREADS),
+                             w3 = __ldg(dk + e + 3 * NTHREADS);
+                j0 = fma(cur[e], w0, j0);
+                j1 = fma(cur[e + NTHREADS], w1, j1);
+                j2 = fma(cur[e + 2 * NTHREADS], w2, j2);
+                j3 = fma(cur[e + 3 * NTHREADS], w3, j3);
+            }
+            for (; e < ne; e += NTHREADS) j0 = fma(cur[e], __ldg(dk + e), j0);
+            jw += (j0 + j1) + (j2 + j3);
+        }
+        if (!roleB) {
+            // A role: va[k] = sum_{l <= k} P[T(k)+l] x[l]
+            for (int k = k0 + tid; k < k1; k += GA) {
+                const double *row = cur + ((k * (k + 1)) / 2 - o0);
+                double ai = 0.0, aj = 0.0, ci = 0.0, cj = 0.0; // two dependency chains per sum
+                int l = 0;
+#pragma unroll 2
+                for (; l + 1 <= k; l += 2) {
+                    const double g0 = row[l], g1 = row[l + 1];
+                    const double2 x0 = x2[l], x1 = x2[l + 1];
+                    ai = fma(g0, x0.x, ai);
+                    aj = fma(g0, x0.y, aj);
+                    ci = fma(g1, x1.x, ci);
+                    cj = fma(g1, x1.y, cj);
+                }
+                if (l <= k) {
+                    const double g0 = row[l];
+                    const double2 x0 = x2[l];
+                    ai = fma(g0, x0.x, ai);
+                    aj = fma(g0, x0.y, aj);
+                }
+                va2[k] = make_double2(ai + ci, aj + cj);
+            }
+        } else {
+            // B role: vb[l] += sum_{k > l} P[T(k)+l] x[k]
+#pragma unroll
+            for (int q = 0; q < QMAX; ++q) {
+                const int l = tb + GB * q;
+                if (l < k1 && l < nmo) {
+                    double si = bi[q], sj = bj[q], ti = 0.0, tj = 0.0; // two dependency chains per sum
+                    int k = (l + 1 > k0 ? l + 1 : k0);
+                    int off = (k * (k + 1)) / 2 - o0 + l;
+#pragma unroll 2
+                    for (; k + 1 < k1; k += 2) {
+                        const double g0 = cur[off], g1 = cur[off + k + 1];
+                        const double2 x0 = x2[k], x1 = x2[k + 1];
+                        si = fma(g0, x0.x, si);
+                        sj = fma(g0, x0.y, sj);
+                        ti = fma(g1, x1.x, ti);
+                        tj = fma(g1, x1.y, tj);
+                        off += 2 * k + 3;
+                    }
+                    if (k < k1) {
+                        const double g0 = cur[off];
+                        const double2 x0 = x2[k];
+                        si = fma(g0, x0.x, si);
+                        sj = fma(g0, x0.y, sj);
+                    }
+                    bi[q] = si + ti;
+                    bj[q] = sj + tj;
+                }
             }
         }
-        __syncthreads(); // the chunk buffer is free; A-term results visible
+        __syncthreads(); // the chunk buffer is free; A-role results visible
 
         if (c == nch - 1) {
-            // column finished.  v_x[l] = va[l] + sum over the warps' private B-term accumulators, in a fixed order,
-            // through the chunk buffer that was just consumed (the prefetch in flight targets the other one)
+            // column finished: the B-role thread that owns column l adds the A-role result of row l
+            if (roleB) {
+#pragma unroll
+                for (int q = 0; q < QMAX; ++q) {
+                    const int l = tb + GB * q;
+                    if (l < nmo) {
+                        const double2 va = va2[l];
+                        p.R1[r * nmo + l] = va.y + bj[q];
+                        p.R2[r * nmo + l] = va.x + bi[q];
+                    }
+                }
+            }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) jw += __shfl_xor_sync(0xffffffffu, jw, o);
-            if (lane == 0) {
-                p.Jp[r * JK_MAXWARPS + warp] = jw;
-                if (NWARPS < JK_MAXWARPS) p.Jp[r * JK_MAXWARPS + warp + NWARPS] = 0.0;
-            }
-            double *red = curbuf;
-#pragma unroll
-            for (int pass = 0; pass < 2; ++pass) { // 0: x = D[:,i] -> R2,  1: x = D[:,j] -> R1
-#pragma unroll
-                for (int m = 0; m < MMAX; ++m) red[warp * NP + lane + 32 * m] = pass ? vbj[m] : vbi[m];
-                __syncthreads();
-                for (int l = tid; l < nmo; l += NTHREADS) {
-                    double sacc = pass ? va2[l].y : va2[l].x;
-#pragma unroll
-                    for (int w = 0; w < NWARPS; ++w) sacc += red[w * NP + l];
-                    (pass ? p.R1 : p.R2)[r * nmo + l] = sacc;
-                }
-                __syncthreads();
-            }
+            if (lane == 0) p.Jp[r * JK_MAXWARPS + warp] = jw;
+            // va2 / x2 are rewritten only behind the next __syncthreads (va2) or at the top of the next column (x2, read
+            // for the last time before the trailing barrier above)
         }
         r = rn;
         c = cn;
@@ -211,14 +225,14 @@ int jk_max_nmo() { return JK_NMO_MAX; }
 int jk_chunk_doubles() { return JK_CHUNK; }
 
 namespace {
-template <int MMAX, int NTHREADS>
+template <int QMAX>
 cudaError_t launch_rows(const JkParams &p, int num_sms, cudaStream_t s)
 {
     const int smem = 2 * JK_BUF * 8 + 2 * JK_NMO_MAX * 16;
-    cudaError_t e = cudaFuncSetAttribute(jk_rows_kernel<MMAX, NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(jk_rows_kernel<QMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     const int grid = p.npair < num_sms ? (int)p.npair : num_sms;
-    jk_rows_kernel<MMAX, NTHREADS><<<grid, NTHREADS, smem, s>>>(p);
+    jk_rows_kernel<QMAX><<<grid, 512, smem, s>>>(p);
     return cudaGetLastError();
 }
 } // namespace
@@ -229,11 +243,11 @@ cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int 
     if (p.nmo > JK_NMO_MAX) return cudaErrorInvalidValue;
     cudaError_t e;
     if (p.nmo <= 256)
-        e = launch_rows<8, 512>(p, num_sms, s);
+        e = launch_rows<1>(p, num_sms, s);
     else if (p.nmo <= 512)
-        e = launch_rows<16, 512>(p, num_sms, s);
+        e = launch_rows<2>(p, num_sms, s);
     else
-        e = launch_rows<24, 256>(p, num_sms, s);
+        e = launch_rows<3>(p, num_sms, s);
     if (e != cudaSuccess) return e;
     dim3 g2((p.nmo + 127) / 128, p.nmo);
     jk_reduce_kernel<<<g2, 128, 0, s>>>(p, J, K, ldo);
