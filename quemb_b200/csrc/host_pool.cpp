@@ -76,7 +76,10 @@ static int default_threads()
     cpu_set_t set;
     if (sched_getaffinity(0, sizeof(set), &set) == 0) n = CPU_COUNT(&set);
     if (n <= 0) n = (int)std::thread::hardware_concurrency();
-    return std::min(std::max(n - 1, 1), 32);
+    // one process per GPU (torchrun sets LOCAL_WORLD_SIZE): the ranks of a node share its cores and memory bandwidth
+    int ranks = 1;
+    if (const char *e = std::getenv("LOCAL_WORLD_SIZE")) ranks = std::max(1, std::atoi(e));
+    return std::min(std::max((n - 1) / ranks, 2), 32);
 }
 
 HostPool &host_pool()
