@@ -167,6 +167,11 @@ int qemb_fragment_transform(qemb_workspace *, const qemb_tensor *, const qemb_me
                             const qemb_screen *, const double *TA_host, int64_t ld, int64_t nao,
                             int64_t nmo, double eps, int64_t p_begin, int64_t p_end, double *out,
                             int64_t ld_out, int out_is_device, int64_t *ticket);
+/* out_is_device == 2: the lower 128x128 tiles of this call's (partial) result are ADDED into `out` with system-scope
+ * red.add.f64 from the K3 epilogue -- `out` may be memory of a PEER GPU opened with qemb_ipc_open, so the reduce-sum of
+ * an aux-sharded fragment rides on NVLink tile by tile while the remaining tiles are still being computed.
+ * The owner zero-fills the matrix first (qemb_device_zero) and rebuilds the upper triangle afterwards
+ * (qemb_device_mirror_lower); ordering between ranks is the caller's (barriers). */
 /* `out` == NULL: (ij|kl) stays resident in the workspace (no device->host transfer); read it with
  * qemb_fragment_get_G / qemb_fragment_G_dev or consume it in place with qemb_fragment_jk. */
 
@@ -208,6 +213,17 @@ int qemb_ctx_launch_count(const qemb_ctx *, int64_t *n);
 /* bytes this context has handed to the copy engines so far: host->device (tensor, metric, S_abs, TA, plan
  * tables) and device->host ((ij|kl) transfers; the screening mask travels through mapped memory) */
 int qemb_ctx_transfer_bytes(const qemb_ctx *, int64_t *h2d, int64_t *d2h);
+
+/* device buffers that other processes of the node can map (cudaIpc*): alloc + 64-byte handle on the owner, open / close
+ * on the peers, free on the owner */
+int qemb_ipc_alloc(qemb_ctx *, int64_t bytes, void **dev, unsigned char *handle64);
+int qemb_ipc_open(qemb_ctx *, const unsigned char *handle64, void **dev);
+int qemb_ipc_close(qemb_ctx *, void *dev);
+int qemb_ipc_free(qemb_ctx *, void *dev);
+/* asynchronous zero fill / upper-from-lower mirror on the context's compute stream; synchronous device -> host copy */
+int qemb_device_zero(qemb_ctx *, void *dev, int64_t bytes);
+int qemb_device_mirror_lower(qemb_ctx *, double *G, int64_t ld, int64_t n);
+int qemb_device_to_host(qemb_ctx *, void *host, const void *dev, int64_t bytes);
 
 /* pinned host memory helpers (so that Python callers can hand out asynchronous buffers) */
 int qemb_host_alloc(void **p, int64_t bytes);

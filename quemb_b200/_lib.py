@@ -117,6 +117,13 @@ _SIGS = {
     "qemb_ctx_mark_elapsed": (c_int, [c_p, c_int, c_int, ctypes.POINTER(ctypes.c_float)]),
     "qemb_ctx_launch_count": (c_int, [c_p, ctypes.POINTER(c_i64)]),
     "qemb_ctx_transfer_bytes": (c_int, [c_p, ctypes.POINTER(c_i64), ctypes.POINTER(c_i64)]),
+    "qemb_ipc_alloc": (c_int, [c_p, c_i64, ctypes.POINTER(c_p), c_p]),
+    "qemb_ipc_open": (c_int, [c_p, c_p, ctypes.POINTER(c_p)]),
+    "qemb_ipc_close": (c_int, [c_p, c_p]),
+    "qemb_ipc_free": (c_int, [c_p, c_p]),
+    "qemb_device_zero": (c_int, [c_p, c_p, c_i64]),
+    "qemb_device_mirror_lower": (c_int, [c_p, c_p, c_i64, c_i64]),
+    "qemb_device_to_host": (c_int, [c_p, c_p, c_p, c_i64]),
     "qemb_host_alloc": (c_int, [ctypes.POINTER(c_p), c_i64]),
     "qemb_host_free": (c_int, [c_p]),
     "qemb_probe_dmma_tflops": (c_int, [c_p, c_i64, c_i64, c_int, ctypes.POINTER(c_dbl)]),

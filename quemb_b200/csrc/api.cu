@@ -1439,7 +1439,7 @@ int solve(qemb_workspace *w, const qemb_metric *m)
 }
 
 // G = X^T X into `dst` (device, ld)
-int gram(qemb_workspace *w, double *dst, int64_t ld)
+int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
 {
     Slot &s = w->slot[w->cur];
     REQ(w->have_sym, "contract_2nd has not run for this fragment");
@@ -1452,7 +1452,8 @@ int gram(qemb_workspace *w, double *dst, int64_t ld)
     p.npair = s.npair;
     p.G = dst;
     p.ldg = ld;
-    const int nsplit = gram_splits(p.ntiles, p.ktiles, w->ctx->num_sms);
+    p.accumulate = accumulate;
+    const int nsplit = accumulate ? 1 : gram_splits(p.ntiles, p.ktiles, w->ctx->num_sms);
     if (nsplit > 1) { // small fragment: fewer tiles than SMs, split the auxiliary index (deterministic two-pass sum)
         TRY(w->gram_partial.reserve((size_t)nsplit * (size_t)s.npair * (size_t)s.npair * 8));
         p.partial = w->gram_partial.as<double>();
@@ -1671,7 +1672,7 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
     TRY(contract_2nd(w));
     if (!t->whitened) TRY(solve(w, m));
     Slot &s = w->slot[w->cur];
-    if (out && out_is_device) return gram(w, out, ld_out);
+    if (out && out_is_device) return gram(w, out, ld_out, out_is_device == 2);
     TRY(gram_ws(w));
     if (!out) return QEMB_OK; // resident: consumers (qemb_fragment_jk, qemb_fragment_get_G) read it in place
     const int gi = w->gi;
@@ -1775,6 +1776,81 @@ extern "C" int qemb_fragment_jk_time(const qemb_workspace *w, float *ms, double 
         const double np = (double)w->slot[w->cur].npair;
         *bytes = 8.0 * np * np;
     }
+    return QEMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// peer memory (aux-sharded fragments: K3 adds its tiles straight into the owner rank's matrix over NVLink)
+// ------------------------------------------------------------------------------------------------
+extern "C" int qemb_ipc_alloc(qemb_ctx *c, int64_t bytes, void **dev, unsigned char *handle64)
+{
+    REQ(c && dev && handle64 && bytes > 0, "bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    DeviceGuard g(c->device);
+    *dev = nullptr;
+    cudaError_t e = cudaMalloc(dev, (size_t)bytes);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(QEMB_ENOMEM, "cudaMalloc of " + std::to_string(bytes) + " bytes failed");
+    }
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, *dev));
+    std::memcpy(handle64, &h, 64);
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ipc_open(qemb_ctx *c, const unsigned char *handle64, void **dev)
+{
+    REQ(c && dev && handle64, "null argument");
+    DeviceGuard g(c->device);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    CU(cudaIpcOpenMemHandle(dev, h, cudaIpcMemLazyEnablePeerAccess));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ipc_close(qemb_ctx *c, void *dev)
+{
+    REQ(c && dev, "null argument");
+    DeviceGuard g(c->device);
+    CU(cudaStreamSynchronize(c->compute));
+    CU(cudaIpcCloseMemHandle(dev));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ipc_free(qemb_ctx *c, void *dev)
+{
+    REQ(c && dev, "null argument");
+    DeviceGuard g(c->device);
+    CU(cudaStreamSynchronize(c->compute));
+    CU(cudaFree(dev));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_device_zero(qemb_ctx *c, void *dev, int64_t bytes)
+{
+    REQ(c && dev && bytes >= 0, "bad argument");
+    DeviceGuard g(c->device);
+    CU(cudaMemsetAsync(dev, 0, (size_t)bytes, c->compute));
+    return QEMB_OK;
+}
+
+extern "C" int qemb_device_mirror_lower(qemb_ctx *c, double *G, int64_t ld, int64_t n)
+{
+    REQ(c && G && ld >= n && n >= 0, "bad argument");
+    DeviceGuard g(c->device);
+    CU(launch_mirror_lower(G, ld, n, c->compute));
+    c->launches += 1;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_device_to_host(qemb_ctx *c, void *host, const void *dev, int64_t bytes)
+{
+    REQ(c && host && dev && bytes >= 0, "bad argument");
+    DeviceGuard g(c->device);
+    CU(cudaMemcpyAsync(host, dev, (size_t)bytes, cudaMemcpyDeviceToHost, c->compute));
+    c->d2h_bytes += bytes;
+    CU(cudaStreamSynchronize(c->compute));
     return QEMB_OK;
 }
 

@@ -90,6 +90,9 @@ struct GramTmaParams {
     // split s writes its partial tile into G + s * split_stride; gram_reduce_kernel adds them up in a fixed order
     int nsplit, kchunk;
     int64_t split_stride;
+    // 1: the lower tiles are ADDED (system-scope red.add.f64) into G, which may live in a peer GPU's memory (NVLink):
+    // the reduce-sum of an aux-sharded fragment happens in the epilogue, tile by tile, while the other tiles compute
+    int accumulate;
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -199,8 +202,12 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
                 for (int e = 0; e < 2; ++e) {
                     if (col + e < p.npair) {
                         const double v = acc.c[i][j][e];
-                        Gout[row + p.ldg * (col + e)] = v;
-                        if (offdiag) Gout[(col + e) + p.ldg * row] = v;
+                        if (p.accumulate) {
+                            atomicAdd_system(&Gout[row + p.ldg * (col + e)], v);
+                        } else {
+                            Gout[row + p.ldg * (col + e)] = v;
+                            if (offdiag) Gout[(col + e) + p.ldg * row] = v;
+                        }
                     }
                 }
             }
@@ -219,6 +226,39 @@ __global__ void gram_reduce_kernel(const double *__restrict__ P, int64_t stride,
         const int64_t c = i / npair, r = i - c * npair;
         G[r + ldg * c] = v;
     }
+}
+
+// G[c, r] = G[r, c] for r > c, 32 x 32 blocks through shared memory (after an accumulated, lower-only K3)
+__global__ void mirror_lower_kernel(double *__restrict__ G, int64_t ld, int64_t n, int nb)
+{
+    __shared__ double t[32][33];
+    // block index -> (bi >= bj) of the lower triangle of 32-blocks
+    const int64_t b = blockIdx.x;
+    int bi = (int)((sqrt(8.0 * (double)b + 1.0) - 1.0) * 0.5);
+    while ((int64_t)(bi + 1) * (bi + 2) / 2 <= b) ++bi;
+    while ((int64_t)bi * (bi + 1) / 2 > b) --bi;
+    const int bj = (int)(b - (int64_t)bi * (bi + 1) / 2);
+    if (bi >= nb) return;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5; // 32 x 8
+    for (int c = ty; c < 32; c += 8) {
+        const int64_t row = (int64_t)bi * 32 + tx, col = (int64_t)bj * 32 + c;
+        t[c][tx] = (row < n && col < n) ? G[row + ld * col] : 0.0;
+    }
+    __syncthreads();
+    for (int c = ty; c < 32; c += 8) {
+        // destination element (row' = bj*32 + tx, col' = bi*32 + c) = source (bi*32 + c, bj*32 + tx) = t[tx][c]
+        const int64_t row = (int64_t)bj * 32 + tx, col = (int64_t)bi * 32 + c;
+        if (row < n && col < n && col > row) G[row + ld * col] = t[tx][c];
+    }
+}
+
+cudaError_t launch_mirror_lower(double *G, int64_t ld, int64_t n, cudaStream_t s)
+{
+    if (n <= 1) return cudaSuccess;
+    const int nb = (int)((n + 31) / 32);
+    const int64_t blocks = (int64_t)nb * (nb + 1) / 2;
+    mirror_lower_kernel<<<(unsigned)blocks, 256, 0, s>>>(G, ld, n, nb);
+    return cudaGetLastError();
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
@@ -268,8 +308,8 @@ cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    const int nsplit = p.partial ? gram_splits(p.ntiles, p.ktiles, num_sms) : 1;
-    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles, 1, p.ktiles, 0};
+    const int nsplit = (p.partial && !p.accumulate) ? gram_splits(p.ntiles, p.ktiles, num_sms) : 1;
+    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles, 1, p.ktiles, 0, p.accumulate};
     if (nsplit > 1) {
         kp.G = p.partial;
         kp.ldg = p.npair;

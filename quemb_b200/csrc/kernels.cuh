@@ -16,7 +16,10 @@ struct GramParams {
     const int2 *tiles; // (ti, tj), ti >= tj, L2-friendly order
     int ntiles;
     double *partial = nullptr; // split-K scratch: gram_splits(...) x npair^2 doubles, or null (no split)
+    int accumulate = 0;        // 1: add the lower tiles into G (system-scope atomics; G may be peer memory), no mirror
 };
+// upper triangle from the lower one, on the device
+cudaError_t launch_mirror_lower(double *G, int64_t ld, int64_t n, cudaStream_t s);
 // number of k splits launch_gram uses when `partial` is given (1 = no split, no scratch needed)
 int gram_splits(int ntiles, int ktiles, int num_sms);
 // TMA + mbarrier pipeline, persistent (one CTA per SM, grid = min(ntiles, num_sms))
