@@ -1848,7 +1848,7 @@ extern "C" int qemb_device_to_host(qemb_ctx *c, void *host, const void *dev, int
 {
     REQ(c && host && dev && bytes >= 0, "bad argument");
     DeviceGuard g(c->device);
-    CU(cudaMemcpyAsync(host, dev, (size_t)bytes, cudaMemcpyDeviceToHost, c->compute));
+    CU(cudaMemcpyAsync(host, dev, (size_t)bytes, cudaMemcpyDefault, c->compute)); // UVA: `host` may be any pointer
     c->d2h_bytes += bytes;
     CU(cudaStreamSynchronize(c->compute));
     return QEMB_OK;

@@ -149,3 +149,124 @@ class AuxShardedBuilder:
             owned.append(i)
             if sink is not None:
                 sink(i, self._to_host(G, npair))
+
+
+class FusedAuxShardedBuilder(AuxShardedBuilder):
+    """Same aux-sharded build, but the reduce-sum is FUSED into K3: every rank's K3 epilogue adds its lower tiles
+    straight into the owner rank's matrix through NVLink peer memory (``qemb_fragment_transform`` with
+    ``out_is_device = 2``: system-scope ``red.add.f64`` from the tile epilogue), so the transfer of a tile overlaps
+    the DMMAs of the following tiles and no separate collective (and no second npair^2 buffer per rank) is needed.
+
+    Per fragment: the owner zero-fills one of its two exported matrices, a barrier publishes that, every rank runs
+    screen / K1 / K2a / K3-accumulate on its slab with the owner's matrix as the target, a second barrier tells
+    the owner that all contributions have landed, and the owner rebuilds the upper triangle on the device
+    (``qemb_device_mirror_lower``).  The matrices are plain ``cudaMalloc`` buffers shared with ``cudaIpc*`` handles,
+    exchanged once through ``all_gather_object``.  The sum order inside a tile entry depends on arrival order for
+    more than two ranks (atomics): results agree with the unsharded path to the 1e-10 budget, not bit for bit.
+    """
+
+    def __init__(self, dist, device: int = 0, group=None):
+        super().__init__(dist, device, group)
+        self._own: list = [None, None]          # this rank's two matrices
+        self._peer: list[list] = []             # [rank][0|1] -> target usable from this process
+        self._cap = 0
+
+    # -- device side (replaced by the CPU tests) -----------------------------------------------------------
+    def _alloc(self, nbytes: int):
+        import ctypes
+
+        from ._lib import c_i64, c_p, check, lib
+
+        dev = c_p()
+        handle = (ctypes.c_ubyte * 64)()
+        check(lib().qemb_ipc_alloc(self.ctx._h, c_i64(nbytes), ctypes.byref(dev), handle))
+        return dev, bytes(handle)
+
+    def _open(self, handle: bytes):
+        import ctypes
+
+        from ._lib import c_p, check, lib
+
+        dev = c_p()
+        buf = (ctypes.c_ubyte * 64).from_buffer_copy(handle)
+        check(lib().qemb_ipc_open(self.ctx._h, buf, ctypes.byref(dev)))
+        return dev
+
+    def _zero(self, target, npair: int) -> None:
+        from ._lib import c_i64, check, lib
+
+        check(lib().qemb_device_zero(self.ctx._h, target, c_i64(8 * npair * npair)))
+        self.ctx.synchronize()
+
+    def _push_partial(self, TA: np.ndarray, eps: float, target, npair: int) -> None:
+        """screen -> K1 -> K2a -> K3 on this rank's slab; K3 ADDS its lower tiles into ``target`` (maybe remote)."""
+        import ctypes
+
+        from . import eri_sparse_DF as q
+        from ._lib import c_dbl, c_i64, c_int, check, lib, ptr
+
+        check(lib().qemb_fragment_transform(
+            self.ws._h, self.tensor._h, None, self.screen._h, ptr(TA), c_i64(q._ld(TA)), c_i64(TA.shape[0]),
+            c_i64(TA.shape[1]), c_dbl(eps), c_i64(0), c_i64(-1), ctypes.cast(target, ctypes.c_void_p), c_i64(npair),
+            c_int(2), None))
+        self.ctx.synchronize()
+
+    def _owner_finish(self, target, npair: int, to_host: bool):
+        from ._lib import c_i64, check, lib, ptr
+
+        check(lib().qemb_device_mirror_lower(self.ctx._h, target, c_i64(npair), c_i64(npair)))
+        if not to_host:
+            self.ctx.synchronize()
+            return None
+        out = np.empty((npair, npair), order="F")
+        check(lib().qemb_device_to_host(self.ctx._h, ptr(out), target, c_i64(8 * npair * npair)))
+        return out
+
+    def _barrier(self) -> None:
+        self.dist.barrier(group=self.group)
+
+    # -- orchestration -----------------------------------------------------------------------------------------
+    def _ensure_targets(self, max_npair: int) -> None:
+        need = 8 * max_npair * max_npair
+        if self._cap >= need:
+            return
+        if self._cap:
+            raise RuntimeError("FusedAuxShardedBuilder: call build() with the largest fragments first or reserve() "
+                               "once; exported matrices are not re-allocated")
+        mine = [self._alloc(need) for _ in range(2)]
+        self._own = [m[0] for m in mine]
+        handles = [None] * self.world
+        self.dist.all_gather_object(handles, [m[1] for m in mine], group=self.group)
+        self._peer = []
+        for rk in range(self.world):
+            self._peer.append(list(self._own) if rk == self.rank else [self._open(h) for h in handles[rk]])
+        self._cap = need
+
+    def reserve(self, max_nmo: int) -> None:
+        """Collective: allocate and exchange the exported matrices for fragments up to ``max_nmo`` orbitals."""
+        self._ensure_targets(max_nmo * (max_nmo + 1) // 2)
+
+    def build(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, sink: Sink | None = None,
+              indices: Sequence[int] | None = None) -> list[int]:
+        idx = list(range(len(TAs))) if indices is None else list(indices)
+        if not idx:
+            return []
+        self.reserve(max(TAs[i].shape[1] for i in idx))
+        owned: list[int] = []
+        for k, i in enumerate(idx):
+            TA = np.asfortranarray(TAs[i], dtype=np.float64)
+            nmo = TA.shape[1]
+            npair = nmo * (nmo + 1) // 2
+            owner = owner_of(k, self.world)
+            target = self._peer[owner][(k // self.world) & 1]
+            if owner == self.rank:
+                self._zero(target, npair)
+            self._barrier()  # the owner's matrix is zero and nobody still reads its previous content
+            self._push_partial(TA, MO_coeff_epsilon, target, npair)
+            self._barrier()  # every rank's tiles have been added
+            if owner == self.rank:
+                owned.append(i)
+                G = self._owner_finish(target, npair, sink is not None)
+                if sink is not None:
+                    sink(i, G)
+        return owned

@@ -25,7 +25,7 @@ import torch.distributed as dist
 
 from quemb_b200 import eri_sparse_DF as q
 from quemb_b200 import synthetic as syn
-from quemb_b200.sharded import AuxShardedBuilder
+from quemb_b200.sharded import AuxShardedBuilder, FusedAuxShardedBuilder
 
 
 def gpu_matmul(A, B):
@@ -78,12 +78,37 @@ class DeviceSinkBuilder(AuxShardedBuilder):
         return G
 
 
+class PeerMatrixView:
+    """Slices of an exported matrix as torch tensors (device copies of the slice only: no second npair^2 buffer)."""
+
+    def __init__(self, ctx, target):
+        self.ctx, self.target = ctx, target
+
+    def __getitem__(self, sl):
+        from quemb_b200._lib import c_i64, c_p, check, lib
+
+        n = sl.stop - sl.start
+        out = torch.empty(n, dtype=torch.float64, device="cuda")
+        check(lib().qemb_device_to_host(self.ctx._h, c_p(out.data_ptr()), c_p(self.target.value + 8 * sl.start), c_i64(8 * n)))
+        return out
+
+
+class FusedDeviceSinkBuilder(FusedAuxShardedBuilder):
+    def _owner_finish(self, target, npair, to_host):  # mirror on the device; the matrix stays where it is
+        from quemb_b200._lib import c_i64, check, lib
+
+        check(lib().qemb_device_mirror_lower(self.ctx._h, target, c_i64(npair), c_i64(npair)))
+        self.ctx.synchronize()
+        return PeerMatrixView(self.ctx, target) if to_host else None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--case", default="chain400")
     ap.add_argument("--frags", type=int, default=2)
     ap.add_argument("--max-gb", type=float, default=6.0)
     ap.add_argument("--out", default="gpurun_out/sharded.json")
+    ap.add_argument("--fused", action="store_true", help="K3 adds its tiles into the owner's matrix over NVLink peer memory")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -103,7 +128,7 @@ def main():
     nmo = TAs[frags[0]].shape[1]
     npair = nmo * (nmo + 1) // 2
 
-    b = DeviceSinkBuilder(dist, device=local)
+    b = (FusedDeviceSinkBuilder if args.fused else DeviceSinkBuilder)(dist, device=local)
     t0 = time.time()
     b.stage(p.unique_dense_data, shape, p.exch_reachable, p.L_PQ, p.S_abs)
     sync()
@@ -128,8 +153,9 @@ def main():
         err = 0.0
         step = 1 << 28
         for o in range(0, npair * npair, step):  # chunked: no third npair^2 temporary
-            err = max(err, float((Gs[o:o + step] - G1[o:o + step]).abs().max()))
-        gmax = float(G1.abs().max())
+            e = min(npair * npair, o + step)
+            err = max(err, float((Gs[o:e] - G1[o:e]).abs().max()))
+        gmax = max(float(G1[o:o + step].abs().max()) for o in range(0, npair * npair, step))
         del G1
     kept.clear()
     sync()
@@ -144,6 +170,7 @@ def main():
     dist.all_reduce(t_sh, op=dist.ReduceOp.MAX)
     slab_bytes = b.tensor.nonzero_size * 8
     b._G = [None, None]
+    kept.clear()
     torch.cuda.empty_cache()
     t_un = None
     if rank == 0:
@@ -156,7 +183,7 @@ def main():
             b.ctx.synchronize()
             t_un = time.perf_counter() - t0
         flops = p.naux * float(npair) * (npair + 1) * len(frags)
-        line = {"case": args.case, "world": world, "nao": p.nao, "naux": p.naux, "nmo": nmo, "npair": npair,
+        line = {"case": args.case, "world": world, "reduce": "fused K3 epilogue -> peer memory (red.add.f64 over NVLink)" if args.fused else "NCCL reduce (async, overlapped with the next fragment)", "nao": p.nao, "naux": p.naux, "nmo": nmo, "npair": npair,
                 "n_unique": p.n_unique, "sigma": round(sigma, 3), "fragments": len(frags), "slabs": b.slab,
                 "slab_tensor_gb": slab_bytes / 1e9, "full_tensor_gb": p.unique_dense_data.nbytes / 1e9,
                 "G_gb": npair * npair * 8 / 1e9, "gen_s": gen_s, "stage_s": stage_s,

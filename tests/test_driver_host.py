@@ -202,3 +202,83 @@ def test_eri_file_container_roundtrip(tmp_path):
             assert f.get("f7") is None and f.keys() == ["f0", "f1"]
             with pytest.raises(OSError):
                 f.create_dataset("f2", data=G)
+
+
+FUSED_WORKER = r"""
+import os, sys, json, fcntl
+sys.path.insert(0, sys.argv[1])
+import numpy as np, scipy.linalg as sla
+import torch.distributed as dist
+from oracle import oracle                      # CPU checker standing in for the device hooks
+from quemb_b200 import synthetic as syn
+from quemb_b200.sharded import FusedAuxShardedBuilder
+
+SCRATCH = sys.argv[2]
+
+class CpuFused(FusedAuxShardedBuilder):
+    # peer memory = a file both processes map; the K3 atomics = read-modify-write under a file lock
+    def _stage_slab(self, M, shape, exch, L, S_abs):
+        p0, p1 = self.slab
+        self.W = np.asfortranarray(sla.solve_triangular(L, M, lower=True)[p0:p1]); self.exch = exch; self.S_abs = S_abs
+    def _alloc(self, nbytes):
+        path = os.path.join(SCRATCH, f"g_{self.rank}_{len(os.listdir(SCRATCH))}.bin")
+        m = np.memmap(path, dtype=np.float64, mode="w+", shape=(nbytes // 8,))
+        return m, path.encode()
+    def _open(self, handle):
+        return np.memmap(handle.decode(), dtype=np.float64, mode="r+")
+    def _zero(self, target, npair):
+        target[: npair * npair] = 0.0; target.flush()
+    def _push_partial(self, TA, eps, target, npair):
+        G = oracle.transform_integral(self.W, self.exch, TA, self.S_abs, np.eye(self.W.shape[0]), eps)
+        low = np.tril(np.ones((npair, npair), dtype=bool))            # lower tiles only, like the kernel
+        with open(os.path.join(SCRATCH, "lock"), "w") as lk:
+            fcntl.flock(lk, fcntl.LOCK_EX)
+            v = np.asarray(target[: npair * npair]).reshape(npair, npair).copy()
+            v[low] += np.asarray(G)[low]
+            target[: npair * npair] = v.reshape(-1); target.flush()
+            fcntl.flock(lk, fcntl.LOCK_UN)
+    def _owner_finish(self, target, npair, to_host):
+        G = np.array(target[: npair * npair]).reshape(npair, npair)
+        G = np.tril(G) + np.tril(G, -1).T
+        return G
+
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+p = syn.make_chain_problem(n_units=6, ao_per_unit=6, n_end=1, naux=88, frag_halfwidth=1, n_bath=6, sigma=0.5, seed=6)
+b = CpuFused(dist, device=0)
+b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+errs = {}
+def sink(i, G):
+    ref = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, p.TAs[i], p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+    errs[i] = float(np.abs(G - ref).max())
+owned = b.build(p.TAs, p.MO_coeff_epsilon, sink)
+out = [None] * world
+dist.all_gather_object(out, {"rank": rank, "owned": owned, "errs": errs})
+if rank == 0:
+    print(json.dumps({"ranks": out, "nfrag": len(p.TAs)}))
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_gloo_fused_peer_accumulate(tmp_path):
+    """Orchestration of the fused K3 -> peer-memory reduction (zero / barrier / accumulate / barrier / mirror, two
+    exported matrices per rank, rotating owners) with file-backed shared memory standing in for NVLink."""
+    script = tmp_path / "fused_worker.py"
+    script.write_text(FUSED_WORKER)
+    scratch = tmp_path / "shm"
+    scratch.mkdir()
+    port = _free_port()
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), OMP_NUM_THREADS="2")
+        procs.append(subprocess.Popen([sys.executable, str(script), str(ROOT), str(scratch)], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=240) for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    res = json.loads(outs[0][0].strip().splitlines()[-1])
+    r0, r1 = res["ranks"]
+    assert sorted(r0["owned"] + r1["owned"]) == list(range(res["nfrag"]))
+    errs = {**r0["errs"], **r1["errs"]}
+    assert len(errs) == res["nfrag"] and max(errs.values()) <= 1e-10, errs

@@ -464,3 +464,56 @@ def test_block_staging_replaces_the_python_scatter_loop(q, name):
     np.testing.assert_array_equal(T.unique_dense_data, g.M)
     fr = g.frag(0)
     assert np.abs(q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps) - fr["G"]).max() <= TOL
+
+
+def test_fused_peer_accumulate_two_gpus(q):
+    """K3 epilogue adds its tiles into the owner rank's matrix over NVLink peer memory (no separate collective):
+    torchrun, one rank per GPU, compared with the oracle on the owner of every fragment."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    if _lib.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+         "--master-port", "29642", str(root / "tests" / "mgpu_fused_worker.py")],
+        capture_output=True, text=True, timeout=600, env=dict(os.environ, PYTHONPATH=str(root)))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "FUSED_OK" in r.stdout
+
+
+def test_accumulate_mode_and_device_mirror_single_gpu(q):
+    """out_is_device = 2 on one device: two slabs accumulated into one zeroed matrix + device mirror = the oracle's
+    (ij|kl); exercises the red.add epilogue, qemb_device_zero / _mirror_lower / _to_host and the IPC allocator."""
+    import ctypes
+
+    from quemb_b200._lib import c_dbl, c_i64, c_int, c_p, check, lib, ptr
+    from quemb_b200.sharded import aux_slabs
+
+    p = syn.make_chain_problem(n_units=10, ao_per_unit=12, n_end=3, naux=333, frag_halfwidth=1, n_bath=20, sigma=0.7,
+                               cond=1e8, seed=111)
+    ctx = q.default_context()
+    ws = q.default_workspace(ctx)
+    L = q.GPU_MatrixHandle(p.L_PQ)
+    Ts = [q.SemiSparseSym3DTensor.whitened_slab(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, L, s)
+          for s in aux_slabs(p.naux, 2)]
+    TA = p.TAs[5]
+    nmo = TA.shape[1]
+    npair = nmo * (nmo + 1) // 2
+    dev, handle = c_p(), (ctypes.c_ubyte * 64)()
+    check(lib().qemb_ipc_alloc(ctx._h, c_i64(8 * npair * npair), ctypes.byref(dev), handle))
+    check(lib().qemb_device_zero(ctx._h, dev, c_i64(8 * npair * npair)))
+    sc = q._screen_for(p.S_abs, ctx)
+    for T in Ts:
+        check(lib().qemb_fragment_transform(ws._h, T._h, None, sc._h, ptr(TA), c_i64(TA.shape[0]), c_i64(TA.shape[0]),
+                                            c_i64(nmo), c_dbl(p.MO_coeff_epsilon), c_i64(0), c_i64(-1), dev, c_i64(npair),
+                                            c_int(2), None))
+    check(lib().qemb_device_mirror_lower(ctx._h, dev, c_i64(npair), c_i64(npair)))
+    G = np.empty((npair, npair), order="F")
+    check(lib().qemb_device_to_host(ctx._h, ptr(G), dev, c_i64(8 * npair * npair)))
+    check(lib().qemb_ipc_free(ctx._h, dev))
+    assert np.array_equal(G, G.T)
+    assert np.abs(G - _oracle_G(p, TA)).max() <= TOL
