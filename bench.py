@@ -291,7 +291,10 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
 
     def device_step(collect: bool):
         work_t.copy_data_from(raw)
-        work_t.whiten(b.metric)
+        if dist is None:
+            work_t.whiten(b.metric)
+        else:  # every rank needs the whole whitened tensor: 1/N of the solve each + NCCL broadcasts over NVLink
+            work_t.whiten_distributed(b.metric, dist)
         for i in mine:
             b.build_device(p.TAs, p.MO_coeff_epsilon, Gdev.data_ptr(), indices=[i])
             if collect:  # per-kernel CUDA-event times of this fragment (waits for it: not used in timed steps)
@@ -407,7 +410,9 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_desc(p),
                    "l2": "inputs larger than L2: whitened (P|mu nu) 2.4 GB, X 0.4-0.55 GB and G 1.1-5.2 GB per fragment",
-                   "partition": f"LPT over {world} rank(s), no data-path collective",
+                   "partition": (f"fragments LPT over {world} rank(s), no collective on the fragment path; the one-off metric "
+                                 "application is split over the ranks by columns and exchanged with NCCL broadcasts"
+                                 if world > 1 else "1 rank"),
                    "fragments_rank0": len(mine)},
         "fragments_per_s": nfrag / t_dev,
         "roofline": {"bound": "tensor", "kernel": "gram_kernel (K3: G = X^T X, FP64 DMMA.8x8x4)",

@@ -98,6 +98,12 @@ void qemb_metric_destroy(qemb_metric *);
  * device copy; afterwards qemb_fragment_transform skips the per-fragment solve (cpp:615). */
 int qemb_tensor_whiten(qemb_tensor *, const qemb_metric *);
 int qemb_tensor_is_whitened(const qemb_tensor *, int *flag);
+/* The same solve on the column range [col0, col0+ncols) only (asynchronous): ranks that each hold a replica of
+ * (P|mu nu) split the columns, exchange the results on the device (qemb_tensor_data_dev gives the address for the
+ * collective) and then declare the tensor whitened. */
+int qemb_tensor_whiten_range(qemb_tensor *, const qemb_metric *, int64_t col0, int64_t ncols);
+int qemb_tensor_set_whitened(qemb_tensor *, int flag);
+int qemb_tensor_data_dev(const qemb_tensor *, void **dev, int64_t *ld);
 /* Aux-sharded staging (oversize fragments): `slab` is a tensor created with naux = the number of
  * auxiliary rows this device owns; the call uploads columns [col0, col0+ncols) of the FULL-naux host matrix
  * (rows >= p_begin + slab naux never travel), solves them against L in a scratch buffer and keeps rows

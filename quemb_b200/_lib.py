@@ -79,6 +79,9 @@ _SIGS = {
     "qemb_metric_create": (c_int, [c_p, c_p, c_i64, c_i64, ctypes.POINTER(c_p)]),
     "qemb_metric_destroy": (None, [c_p]),
     "qemb_tensor_whiten": (c_int, [c_p, c_p]),
+    "qemb_tensor_whiten_range": (c_int, [c_p, c_p, c_i64, c_i64]),
+    "qemb_tensor_set_whitened": (c_int, [c_p, c_int]),
+    "qemb_tensor_data_dev": (c_int, [c_p, ctypes.POINTER(c_p), ctypes.POINTER(c_i64)]),
     "qemb_tensor_is_whitened": (c_int, [c_p, ctypes.POINTER(c_int)]),
     "qemb_screen_create": (c_int, [c_p, c_p, c_i64, c_i64, ctypes.POINTER(c_p)]),
     "qemb_screen_destroy": (None, [c_p]),

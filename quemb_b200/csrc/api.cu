@@ -867,6 +867,48 @@ extern "C" int qemb_tensor_release_scratch(qemb_tensor *t)
     return QEMB_OK;
 }
 
+// Column range of the one-off metric application (design option O1), for ranks that split the columns of (P|mu nu)
+// among themselves and exchange the results (bench.py --gpus N: every rank needs the whole whitened tensor, but
+// only 1/N of the naux^2 n_unique flops).  The tensor is marked whitened by qemb_tensor_set_whitened once the
+// caller has gathered all ranges.
+extern "C" int qemb_tensor_whiten_range(qemb_tensor *t, const qemb_metric *m, int64_t col0, int64_t ncols)
+{
+    REQ(t && m, "null argument");
+    REQ(t->ctx == m->ctx, "tensor and metric live on different contexts");
+    REQ(t->naux == m->naux, "naux mismatch between tensor and metric");
+    REQ(!t->whitened, "tensor is already whitened");
+    REQ(col0 >= 0 && ncols >= 0 && col0 + ncols <= t->n_unique, "column range outside the tensor");
+    if (ncols == 0) return QEMB_OK;
+    DeviceGuard g(t->ctx->device);
+    TrsmParams p;
+    p.L = m->L.as<double>();
+    p.ldl = m->naux_pad;
+    p.Dinv = m->Dinv.as<double>();
+    p.nblocks = m->nblocks;
+    p.X = t->data.as<double>() + col0 * t->ldp;
+    p.ldx = t->ldp;
+    p.ncol = ncols;
+    CU(launch_trsm_rows(p, (int)t->naux16, t->ctx->compute));
+    t->ctx->launches += 1;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_tensor_set_whitened(qemb_tensor *t, int flag)
+{
+    REQ(t, "null tensor");
+    t->whitened = flag != 0;
+    return QEMB_OK;
+}
+
+// device address and leading dimension (in doubles) of the ldp x n_unique data, for collectives on it
+extern "C" int qemb_tensor_data_dev(const qemb_tensor *t, void **dev, int64_t *ld)
+{
+    REQ(t && dev, "null argument");
+    *dev = t->data.p;
+    if (ld) *ld = t->ldp;
+    return QEMB_OK;
+}
+
 extern "C" int qemb_tensor_copy_data(qemb_tensor *dst, const qemb_tensor *src)
 {
     REQ(dst && src, "null argument");

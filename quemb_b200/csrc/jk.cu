@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(512, 1) jk_rows_kernel(JkParams p)
                 const double *row = cur + ((k * (k + 1)) / 2 - o0);
                 double ai = 0.0, aj = 0.0, ci = 0.0, cj = 0.0; // two dependency chains per sum
                 int l = 0;
-#pragma unroll 2
+#pragma unroll 4
                 for (; l + 1 <= k; l += 2) {
                     const double g0 = row[l], g1 = row[l + 1];
                     const double2 x0 = x2[l], x1 = x2[l + 1];
@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(512, 1) jk_rows_kernel(JkParams p)
                     double si = bi[q], sj = bj[q], ti = 0.0, tj = 0.0; // two dependency chains per sum
                     int k = (l + 1 > k0 ? l + 1 : k0);
                     int off = (k * (k + 1)) / 2 - o0 + l;
-#pragma unroll 2
+#pragma unroll 4
                     for (; k + 1 < k1; k += 2) {
                         const double g0 = cur[off], g1 = cur[off + k + 1];
                         const double2 x0 = x2[k], x1 = x2[k + 1];

@@ -418,6 +418,38 @@ class SemiSparseSym3DTensor:
         t.p_range = (p0, p1)
         return t
 
+    def whiten_distributed(self, L_PQ, dist, group=None) -> None:
+        """``whiten`` for ranks that each hold a replica of (P|mu nu) (fragment-parallel builds): rank r solves only
+        its 1/world share of the columns and the shares are exchanged in place with one NCCL broadcast per rank
+        (NVLink), instead of every rank repeating all ``naux^2 n_unique`` flops."""
+        import torch  # noqa: PLC0415
+
+        self._flush()
+        m = _metric_for(L_PQ, self.ctx)
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        bounds = [(self._n_unique * r) // world for r in range(world + 1)]
+        check(lib().qemb_tensor_whiten_range(self._h, m._h, c_i64(bounds[rank]), c_i64(bounds[rank + 1] - bounds[rank])))
+        dev, ld = c_p(), c_i64()
+        check(lib().qemb_tensor_data_dev(self._h, ctypes.byref(dev), ctypes.byref(ld)))
+        self.ctx.synchronize()  # the collective runs on torch's stream
+
+        class _View:  # CUDA array interface over the library's device memory
+            def __init__(self, ptr_, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr_, False), "version": 2}
+
+        works = []
+        for r in range(world):
+            n = (bounds[r + 1] - bounds[r]) * ld.value
+            if n == 0:
+                continue
+            view = torch.as_tensor(_View(dev.value + 8 * bounds[r] * ld.value, n), device=torch.device("cuda", self.ctx.device))
+            src = r if group is None else dist.get_global_rank(group, r)
+            works.append(dist.broadcast(view, src=src, group=group, async_op=True))
+        for w in works:
+            w.wait()
+        torch.cuda.current_stream(self.ctx.device).synchronize()
+        check(lib().qemb_tensor_set_whitened(self._h, c_int(1)))
+
     def copy_data_from(self, other: "SemiSparseSym3DTensor") -> None:
         """Device-to-device copy of the data of a tensor built from the same lists."""
         other._flush()

@@ -33,6 +33,14 @@ def sink(i, G):
 
 
 owned = b.build(p.TAs, p.MO_coeff_epsilon, sink)
+
+# column-split metric application with NCCL broadcasts == the single-rank one, bit for bit (same kernel per column)
+from quemb_b200 import eri_sparse_DF as q
+Ta = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, ctx=b.ctx)
+Tb = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, ctx=b.ctx)
+Ta.whiten(p.L_PQ)
+Tb.whiten_distributed(p.L_PQ, dist)
+assert Tb.whitened and np.array_equal(Ta.unique_dense_data, Tb.unique_dense_data), "whiten_distributed differs"
 out = [None] * world
 dist.all_gather_object(out, {"rank": rank, "owned": owned, "errs": errs, "slab": b.slab})
 if rank == 0:
