@@ -204,6 +204,10 @@ int qemb_ctx_set_timing(qemb_ctx *, int enabled);
  * fragment are in flight (the reference's GPU variant copies the full syrk result and mirrors it on one
  * host thread, cpp:684-708).  0: the full square crosses PCIe. */
 int qemb_ctx_set_output_mode(qemb_ctx *, int mode);
+/* Output mode 1 only: the last `frac` of the columns of a host-bound (ij|kl) cross PCIe whole and are not mirrored by
+ * the host threads (default: QEMB_FULL_COLUMN_FRACTION or 0).  Shifts work from the host cores (the bottleneck of the
+ * pure triangle transfer) to the copy engine, which has slack while the kernels run. */
+int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
 /* number of host worker threads of the library (QEMB_HOST_THREADS, default: cores in the affinity mask - 1) */
 int qemb_host_threads(int *n);
 /* G[c + ld*r] = G[r + ld*c] for all r > c of an n x n host matrix (the host half of output mode 1; also the

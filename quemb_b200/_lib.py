@@ -113,6 +113,7 @@ _SIGS = {
     "qemb_fragment_work": (c_int, [c_p, c_p, c_p]),
     "qemb_ctx_set_timing": (c_int, [c_p, c_int]),
     "qemb_ctx_set_output_mode": (c_int, [c_p, c_int]),
+    "qemb_ctx_set_full_column_fraction": (c_int, [c_p, c_dbl]),
     "qemb_host_threads": (c_int, [ctypes.POINTER(c_int)]),
     "qemb_host_mirror_lower": (c_int, [c_p, c_i64, c_i64]),
     "qemb_fragment_times": (c_int, [c_p, c_p]),

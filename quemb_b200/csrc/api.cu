@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <condition_variable>
 #include <cstring>
 #include <limits>
@@ -74,6 +75,9 @@ struct qemb_ctx {
     // how a host-bound G travels: 1 = lower triangle over PCIe + mirror on the host cores (default),
     // 0 = the full square over PCIe
     int out_mode = 1;
+    // mode 1 only: the last `full_frac` of the columns cross PCIe whole (rows 0..n) and are not mirrored on the host:
+    // balances the copy engine (slack) against the host threads (the bottleneck of a pure triangle transfer)
+    double full_frac = 0.0;
     int num_sms = 148;
     int64_t h2d_bytes = 0, d2h_bytes = 0; // bytes handed to the copy engines (uploads / G transfers)
     // host-bound G transfers whose host mirror has not finished yet (qemb_ctx_synchronize waits for them)
@@ -365,6 +369,7 @@ extern "C" int qemb_ctx_create(int device, qemb_ctx **out)
     if (!c) return fail(QEMB_ENOMEM, "host allocation failed");
     c->device = device;
     c->num_sms = prop.multiProcessorCount;
+    if (const char *e = std::getenv("QEMB_FULL_COLUMN_FRACTION")) c->full_frac = std::min(1.0, std::max(0.0, std::atof(e)));
     CU(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->prep, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
@@ -424,6 +429,13 @@ extern "C" int qemb_ctx_set_output_mode(qemb_ctx *c, int mode)
     REQ(c != nullptr, "null ctx");
     REQ(mode == 0 || mode == 1, "output mode must be 0 (full square over PCIe) or 1 (lower triangle + host mirror)");
     c->out_mode = mode;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_set_full_column_fraction(qemb_ctx *c, double frac)
+{
+    REQ(c && frac >= 0.0 && frac <= 1.0, "fraction must be in [0, 1]");
+    c->full_frac = frac;
     return QEMB_OK;
 }
 
@@ -1622,6 +1634,7 @@ struct MirrorCb {
     double *out;
     int64_t ld, n, c0, c1;
     bool last;
+    int64_t cs; // columns >= cs arrive whole over PCIe: mirror destinations stop there
 };
 
 // runs on a driver thread once the copy group [c0, c1) has landed: hand its mirror work to the pool
@@ -1630,7 +1643,8 @@ void CUDART_CB mirror_callback(void *arg)
     MirrorCb *cb = static_cast<MirrorCb *>(arg);
     OutJob *job = cb->job;
     const int64_t width = cb->c1 - cb->c0;
-    const int64_t rows = cb->n - cb->c1; // rows strictly below the group's diagonal block
+    const int64_t rows = std::max<int64_t>(0, cb->cs - cb->c1); // rows below the group's diagonal block whose
+                                                                 // transposed image is not delivered by PCIe
     int64_t chunk = 0, ntasks = 0;
     if (rows > 0 && width > 0) {
         chunk = std::max<int64_t>(256, ((int64_t)(2 << 20) / (8 * width) + 15) / 16 * 16); // ~2 MB per task
@@ -1642,7 +1656,7 @@ void CUDART_CB mirror_callback(void *arg)
         if (job->remaining == 0) job_finished(*job);
     }
     double *out = cb->out;
-    const int64_t ld = cb->ld, n = cb->n, c0 = cb->c0, c1 = cb->c1;
+    const int64_t ld = cb->ld, n = cb->cs, c0 = cb->c0, c1 = cb->c1;
     for (int64_t t = 0; t < ntasks; ++t) {
         const int64_t r0 = c1 + t * chunk, r1 = std::min(n, r0 + chunk);
         host_pool().submit([=] {
@@ -1674,15 +1688,21 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         w->ctx->out_pending += 1;
     }
     const int64_t target = 64ll << 20;
+    // column split: [0, csplit) travel as lower triangle + host mirror, [csplit, n) whole
+    int64_t csplit = n;
+    if (w->ctx->full_frac > 0.0) csplit = std::max<int64_t>(0, (int64_t)((1.0 - w->ctx->full_frac) * (double)n) / 256 * 256);
     for (int64_t c0 = 0; c0 < n;) {
-        const int64_t rows = n - c0;
+        const bool whole = c0 >= csplit;
+        const int64_t r_first = whole ? 0 : c0;
+        const int64_t rows = n - r_first;
         int64_t width = std::max<int64_t>(256, (target / (8 * rows) + 255) / 256 * 256);
         int64_t c1 = std::min(n, c0 + width);
-        if (n - c1 < 256) c1 = n;
+        if (!whole && c1 > csplit) c1 = csplit; // groups do not straddle the split
+        if (n - c1 < 256 && (whole || csplit == n)) c1 = n;
         w->ctx->d2h_bytes += rows * 8 * (c1 - c0);
-        CU(cudaMemcpy2DAsync(out + c0 + ld_out * c0, (size_t)ld_out * 8, G + c0 + n * c0, (size_t)n * 8, (size_t)rows * 8,
-                             (size_t)(c1 - c0), cudaMemcpyDeviceToHost, cs));
-        MirrorCb *cb = new MirrorCb{&job, out, ld_out, n, c0, c1, c1 == n};
+        CU(cudaMemcpy2DAsync(out + r_first + ld_out * c0, (size_t)ld_out * 8, G + r_first + n * c0, (size_t)n * 8,
+                             (size_t)rows * 8, (size_t)(c1 - c0), cudaMemcpyDeviceToHost, cs));
+        MirrorCb *cb = new MirrorCb{&job, out, ld_out, n, c0, c1, c1 == n, whole ? c1 : csplit};
         cudaError_t e = cudaLaunchHostFunc(cs, mirror_callback, cb);
         if (e != cudaSuccess) {
             delete cb;

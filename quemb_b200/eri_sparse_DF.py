@@ -81,6 +81,11 @@ class Context:
         False: the full square crosses PCIe."""
         check(lib().qemb_ctx_set_output_mode(self._h, c_int(1 if triangle else 0)))
 
+    def set_full_column_fraction(self, frac: float) -> None:
+        """Triangle output mode: the last ``frac`` of the columns travel whole over PCIe instead of being mirrored
+        by the host threads."""
+        check(lib().qemb_ctx_set_full_column_fraction(self._h, c_dbl(frac)))
+
     def set_timing(self, enabled: bool) -> None:
         check(lib().qemb_ctx_set_timing(self._h, c_int(1 if enabled else 0)))
 

@@ -11,11 +11,13 @@ from quemb_b200.driver import FragmentERIBuilder
 tri = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 nb = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 nfrag = int(sys.argv[3]) if len(sys.argv) > 3 else 32
+frac = float(sys.argv[4]) if len(sys.argv) > 4 else 0.0
 p = bench.make_workload("c32h66", use_gpu_matmul=True)
 idx = list(range(len(p.TAs)))[:nfrag]
 b = FragmentERIBuilder(0, n_host_buffers=nb)
 ctx = b.ctx
 ctx.set_output_mode(bool(tri))
+ctx.set_full_column_fraction(frac)
 T = q.SemiSparseSym3DTensor((p.naux, p.nao, p.nao), p.exch_reachable, ctx=ctx)
 b.reserve_host(max(t.shape[1] for t in p.TAs))
 log = []
@@ -37,7 +39,7 @@ for rep in range(3):
     tot = {}
     for k, v in log: tot[k] = tot.get(k, 0) + v
     d2h = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in idx)
-    print(f"rep {rep} tri={tri} nb={nb}: upload {t1-t0:.3f} stage+whiten {t2-t1:.3f} build {t3-t2:.3f} total {t3-t0:.3f} s | "
+    print(f"rep {rep} tri={tri} nb={nb} full_frac={frac}: upload {t1-t0:.3f} stage+whiten {t2-t1:.3f} build {t3-t2:.3f} total {t3-t0:.3f} s | "
           + " ".join(f"{k} {v:.3f}" for k, v in tot.items()) + f" | G bytes {d2h/1e9:.1f} GB -> {d2h/(t3-t2)/1e9:.1f} GB/s effective")
 # symmetry / parity spot check of the last fragment against the full-square mode
 i = idx[-1]; nmo = p.TAs[i].shape[1]; npair = nmo * (nmo + 1) // 2

@@ -517,3 +517,28 @@ def test_accumulate_mode_and_device_mirror_single_gpu(q):
     check(lib().qemb_ipc_free(ctx._h, dev))
     assert np.array_equal(G, G.T)
     assert np.abs(G - _oracle_G(p, TA)).max() <= TOL
+
+
+def test_hybrid_output_transfer_matches_full_square(q):
+    """Host-bound (ij|kl): triangle + host mirror, the hybrid (tail columns whole over PCIe) and the full-square
+    transfer must deliver bit-identical matrices."""
+    p = syn.make_chain_problem(n_units=14, ao_per_unit=24, n_end=5, naux=200, frag_halfwidth=2, n_bath=40,
+                               sigma=0.94, seed=112, n_frag=8)
+    ctx = q.default_context()
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    T.whiten(p.L_PQ)
+    TA = p.TAs[6]
+    try:
+        ctx.set_output_mode(False)
+        G0 = q.transform_integral(T, TA, p.S_abs, None, p.MO_coeff_epsilon).copy()
+        ctx.set_output_mode(True)
+        outs = []
+        for frac in (0.0, 0.07, 0.5, 1.0):
+            ctx.set_full_column_fraction(frac)
+            outs.append(q.transform_integral(T, TA, p.S_abs, None, p.MO_coeff_epsilon).copy())
+    finally:
+        ctx.set_output_mode(True)
+        ctx.set_full_column_fraction(0.0)
+    assert G0.shape[0] > 4096
+    for G in outs:
+        assert np.array_equal(G, G0)
