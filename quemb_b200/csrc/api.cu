@@ -1787,7 +1787,17 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
         crow.push_back((int)nmo);
     }
     const int nch = (int)crow.size() - 1;
-    // inputs: D (nmo^2) | dpk (npair) | crow
+    // single-pass streaming kernel (jk_stream.cu) when the fragment fits it; QEMB_JK_KERNEL=rows forces jk.cu
+    int srow[64] = {0}, nst = 0, ring = 0, stage_doubles = 0, stream_smem = 0;
+    {
+        const char *force = std::getenv("QEMB_JK_KERNEL");
+        const bool want_rows = force && std::strcmp(force, "rows") == 0;
+        if (!want_rows && nmo <= jk_stream_max_nmo() && (reinterpret_cast<uintptr_t>(w->G_last) & 15) == 0)
+            nst = jk_stream_plan((int)nmo, srow, &ring, &stage_doubles, &stream_smem);
+    }
+    const bool stream = nst > 0;
+    if (stream) crow.assign(srow, srow + nst + 1);
+    // inputs: D (nmo^2) | dpk (npair) | crow (jk.cu chunk table or jk_stream.cu stage table)
     const size_t oD = 0, oP = (size_t)nmo * nmo * 8, oC = oP + (size_t)npair * 8;
     const size_t in_bytes = oC + crow.size() * 4;
     std::vector<double> hin((in_bytes + 7) / 8);
@@ -1797,7 +1807,8 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
         for (int64_t l = 0; l <= k; ++l) hin[oP / 8 + k * (k + 1) / 2 + l] = (k == l ? 1.0 : 2.0) * D[k + ldd * l];
     std::memcpy(reinterpret_cast<char *>(hin.data()) + oC, crow.data(), crow.size() * 4);
     TRY(w->jk_in.reserve(in_bytes));
-    const int64_t njp = npair * jk_warps();
+    const int njp1 = stream ? 1 : jk_warps();
+    const int64_t njp = npair * njp1;
     TRY(w->jk_scratch.reserve(((size_t)njp + 2 * (size_t)npair * nmo) * 8));
     TRY(w->jk_out.reserve(2 * (size_t)nmo * nmo * 8));
     CU(cudaMemcpyAsync(w->jk_in.p, hin.data(), in_bytes, cudaMemcpyHostToDevice, cs));
@@ -1811,6 +1822,11 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     p.dpk = reinterpret_cast<const double *>(static_cast<char *>(w->jk_in.p) + oP);
     p.crow = reinterpret_cast<const int *>(static_cast<char *>(w->jk_in.p) + oC);
     p.nchunks = nch;
+    p.srow = p.crow;
+    p.nstages = nst;
+    p.ring = ring;
+    p.stage_doubles = stage_doubles;
+    p.njp = njp1;
     p.Jp = w->jk_scratch.as<double>();
     p.R1 = p.Jp + njp;
     p.R2 = p.R1 + npair * nmo;
@@ -1818,7 +1834,12 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     for (auto &e : w->jk_ev)
         if (!e) CU(cudaEventCreate(&e));
     CU(cudaEventRecord(w->jk_ev[0], cs));
-    CU(launch_jk(p, Jd, Kd, nmo, w->ctx->num_sms, cs));
+    if (stream) {
+        CU(launch_jk_stream(p, stream_smem, w->ctx->num_sms, cs));
+        CU(launch_jk_reduce(p, Jd, Kd, nmo, cs));
+    } else {
+        CU(launch_jk(p, Jd, Kd, nmo, w->ctx->num_sms, cs));
+    }
     CU(cudaEventRecord(w->jk_ev[1], cs));
     w->ctx->launches += 2;
     CU(cudaMemcpy2DAsync(vj, (size_t)ldo * 8, Jd, (size_t)nmo * 8, (size_t)nmo * 8, (size_t)nmo, cudaMemcpyDeviceToHost, cs));

@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(512, 1) jk_rows_kernel(JkParams p)
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) jw += __shfl_xor_sync(0xffffffffu, jw, o);
-            if (lane == 0) p.Jp[r * JK_MAXWARPS + warp] = jw;
+            if (lane == 0) p.Jp[r * p.njp + warp] = jw;
             // va2 / x2 are rewritten only behind the next __syncthreads (va2) or at the top of the next column (x2, read
             // for the last time before the trailing barrier above)
         }
@@ -214,9 +214,9 @@ __global__ void jk_reduce_kernel(JkParams p, double *__restrict__ J, double *__r
     for (int i = a + 1; i < nmo; ++i) s += p.R2[(tri(i) + a) * nmo + k];
     K[a + ldo * k] = s;
     const int hi = a > k ? a : k, lo = a > k ? k : a;
-    const double *jp = p.Jp + (tri(hi) + lo) * JK_MAXWARPS;
+    const double *jp = p.Jp + (tri(hi) + lo) * p.njp;
     double t = 0.0;
-    for (int w = 0; w < JK_MAXWARPS; ++w) t += jp[w];
+    for (int w = 0; w < p.njp; ++w) t += jp[w];
     J[a + ldo * k] = t;
 }
 
@@ -249,6 +249,11 @@ cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int 
     else
         e = launch_rows<3>(p, num_sms, s);
     if (e != cudaSuccess) return e;
+    return launch_jk_reduce(p, J, K, ldo, s);
+}
+
+cudaError_t launch_jk_reduce(const JkParams &p, double *J, double *K, int64_t ldo, cudaStream_t s)
+{
     dim3 g2((p.nmo + 127) / 128, p.nmo);
     jk_reduce_kernel<<<g2, 128, 0, s>>>(p, J, K, ldo);
     return cudaGetLastError();

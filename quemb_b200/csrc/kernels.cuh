@@ -84,13 +84,22 @@ struct JkParams {
     const double *dpk; // packed weights: D[k,l] * (k == l ? 1 : 2) at T(k)+l
     const int *crow;   // chunk table: packed rows [crow[c], crow[c+1]) form chunk c
     int nchunks;
-    double *Jp;        // npair x jk_warps() per-warp partial sums of J
+    double *Jp;        // npair x njp partial sums of J
+    int njp;           // jk_warps() (jk.cu) or 1 (jk_stream.cu)
     double *R1, *R2;   // npair x nmo (row r at r*nmo)
+    // jk_stream.cu: stage table (stage st = packed rows [srow[st], srow[st+1])), ring depth and slot size
+    const int *srow;
+    int nstages, ring, stage_doubles;
 };
 cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int num_sms, cudaStream_t s);
 int jk_max_nmo();
 int jk_chunk_doubles();
 int jk_warps();
+// single-pass streaming kernel (jk_stream.cu), nmo <= jk_stream_max_nmo(), G 16-byte aligned
+int jk_stream_max_nmo();
+int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_bytes);
+cudaError_t launch_jk_stream(const JkParams &p, int smem, int num_sms, cudaStream_t s);
+cudaError_t launch_jk_reduce(const JkParams &p, double *J, double *K, int64_t ldo, cudaStream_t s);
 
 // ---- screening -------------------------------------------------------------------------------------
 // mask[mu + nao*i] = |sum_nu S[mu,nu] TA[nu,i]| >= eps  (left-to-right, no FMA contraction)

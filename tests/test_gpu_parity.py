@@ -293,8 +293,16 @@ def test_octane_full_size_vs_compiled_reference(q):
         assert np.abs(Gw - G_ref).max() <= TOL
 
 
+@pytest.fixture(params=["stream", "rows"])
+def jk_kernel(request, monkeypatch):
+    """Both J/K kernels: the single-pass streaming kernel (jk_stream.cu, default for nmo <= 256) and the chunked
+    row/column kernel (jk.cu, larger fragments); the library reads QEMB_JK_KERNEL on every call."""
+    monkeypatch.setenv("QEMB_JK_KERNEL", request.param)
+    return request.param
+
+
 @pytest.mark.parametrize("name", ["chain_small", "lattice_small"])
-def test_jk_consumer_on_resident_eri(q, name):
+def test_jk_consumer_on_resident_eri(q, name, jk_kernel):
     """Fused consumer: J/K and the HF-in-HF two-electron sum from the device-resident (ij|kl)
     against the CPU restatements applied to the REFERENCE's golden G."""
     from oracle import consumer_oracle as co
@@ -333,7 +341,7 @@ def test_jk_consumer_on_resident_eri(q, name):
         ws.jk(np.triu(np.ones((nmo, nmo))))  # not symmetric
 
 
-def test_jk_multi_chunk_matches_torch(q):
+def test_jk_multi_chunk_matches_torch(q, jk_kernel):
     """nmo large enough for several shared-memory chunks per column (npair > 12288): J/K against a torch FP64
     evaluation from the library's own resident G."""
     import torch
