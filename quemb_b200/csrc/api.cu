@@ -1798,7 +1798,8 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     const bool stream = nst > 0;
     if (stream) crow.assign(srow, srow + nst + 1);
     // inputs: D (nmo^2) | dpk (npair) | crow (jk.cu chunk table or jk_stream.cu stage table)
-    const size_t oD = 0, oP = (size_t)nmo * nmo * 8, oC = oP + (size_t)npair * 8;
+    // (dpk 16-byte aligned and padded by two doubles: jk_stream.cu copies whole rows of it with 16-byte bulk copies)
+    const size_t oD = 0, oP = ((size_t)nmo * nmo * 8 + 15) / 16 * 16, oC = oP + ((size_t)npair + 2) * 8;
     const size_t in_bytes = oC + crow.size() * 4;
     std::vector<double> hin((in_bytes + 7) / 8);
     for (int64_t l = 0; l < nmo; ++l)

@@ -13,10 +13,11 @@
 // along l, conflict free), one row pair costs ~12 instructions per 64 elements plus one 4-value butterfly, and
 // there is no CTA barrier inside a column:
 //   * producer warp: one 1-D bulk copy (cp.async.bulk, SASS UBLKCP) per stage = a block of whole packed rows,
-//     completion counted on the stage's "full" mbarrier; it runs ahead over column boundaries by the ring depth
-//   * 8 consumer warps: wait "full", process their row pairs of the stage, release the PREVIOUS stage after the
-//     next wait (same deferred release as k3_gram.cu: an arrive placed directly behind the loads is scheduled
-//     ahead of the FMAs that consume them)
+//     and one of the same rows of the J weights, completion counted on the stage's "full" mbarrier; stages are
+//     placed back to back in a ring that takes all the shared memory left, so ~100 KB are in flight per SM
+//   * 8 consumer warps: wait "full", process their row pair of the stage, release it behind a store whose data
+//     depends on every read of the stage (an arrive placed directly behind the loads is issued before they return,
+//     the race found in k3_gram.cu)
 //   * per column two named barriers among the consumers: column sums of the 8 warps meet in shared memory and
 //     are added in a fixed order (deterministic), next column's density columns are staged meanwhile
 #include "common.cuh"
@@ -36,8 +37,9 @@ __device__ __forceinline__ void static_for(F &&f)
 }
 constexpr int JS_NW = 8;                      // consumer warps
 constexpr int JS_THREADS = 32 * (JS_NW + 1);  // + producer warp
-constexpr int JS_MAX_RING = 6;
-constexpr int JS_MAX_STAGES = 40;             // stages per column (<= ceil(256 / 8))
+constexpr int JS_NB = 16;                     // mbarrier pairs = stages in flight at most
+constexpr int JS_MAX_STAGES = 40;             // stages per column (<= 2 * 8)
+constexpr int JS_ROWS = 16;                   // packed rows per stage: one row pair per consumer warp
 
 __device__ __forceinline__ int tri32(int k) { return (k * (k + 1)) >> 1; }
 
@@ -88,28 +90,33 @@ __device__ __forceinline__ void pair_of(int64_t r, int &i, int &j)
 }
 } // namespace
 
-// shared memory: ring * stage_doubles doubles | slab[JS_NW][nmoP] double2 | x2[2][nmoP] double2 | va2[nmoP] double2 |
-//                jws[JS_NW] | srow[JS_MAX_STAGES + 1] | full[ring], empty[ring]
+// shared memory: ring of stage_doubles doubles, a stage = [G rows | weight rows] placed back to back (wrapping to 0
+//                when the next one does not fit) | slab[JS_NW][nmoP] double2 | x2[2][nmoP] double2 | va2[nmoP] double2 |
+//                jws[JS_NW] | full[JS_NB], empty[JS_NB]
+// Stage S = packed rows [16 S, min(16 S + 16, nmo)): warp w owns the row pair (16 S + 2 w, + 1).  Every row of the stage
+// has NF = S / 2 blocks of 32 columns strictly left of the diagonal and one block that contains it, so the block
+// structure is a compile-time property of the stage and the stage loop unrolls without data-dependent branches.
 template <int QL>
 __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
 {
     constexpr int NMOP = 32 * QL;
+    constexpr int NSTAGE = 2 * QL; // stages 0 .. 2 QL - 2 always exist (nmo > 32 (QL - 1)), the last one may not
     extern __shared__ __align__(16) double js_smem[];
+    const int cap = p.stage_doubles; // ring capacity in doubles (even); stages are placed back to back
     double *ringbuf = js_smem;
-    double2 *slab = reinterpret_cast<double2 *>(ringbuf + (size_t)p.ring * p.stage_doubles);
+    double2 *slab = reinterpret_cast<double2 *>(ringbuf + cap);
     double2 *x2 = slab + JS_NW * NMOP;
     double2 *va2 = x2 + 2 * NMOP;
     double *jws = reinterpret_cast<double *>(va2 + NMOP);
-    int *srow = reinterpret_cast<int *>(jws + JS_NW);
-    uint64_t *full = reinterpret_cast<uint64_t *>(srow + JS_MAX_STAGES + 2);
-    uint64_t *empty = full + JS_MAX_RING;
+    double *prf = jws + JS_NW; // per-warp sink of the release proofs
+    uint64_t *full = reinterpret_cast<uint64_t *>(prf + JS_NW);
+    uint64_t *empty = full + JS_NB;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nmo = p.nmo, nst = p.nstages, ring = p.ring;
+    const int nmo = p.nmo, nst = p.nstages;
 
-    for (int q = tid; q <= nst; q += JS_THREADS) srow[q] = p.srow[q]; // producer's stage table
     if (tid == 0) {
-        for (int s = 0; s < ring; ++s) {
+        for (int s = 0; s < JS_NB; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], JS_NW);
         }
@@ -121,28 +128,66 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
         // ---------------------------------------------------------------- producer
         if (lane != 0) return;
         const double *Gend = p.G + p.ldg * (p.npair - 1) + p.npair;
-        int s = 0, phase = 0;
+        // Ring bookkeeping in registers: `v` counts doubles handed out since the start (including the gap skipped at
+        // a wrap), `rel` is v at the end of the last stage known to be released.  Stages are released in order, so a
+        // region is free as soon as (its end in v) - rel <= cap.  The released stages' ends are replayed with the same
+        // placement rule instead of being stored.
+        auto stage_size = [&](int st, int colpar, int &cnt, int &cntw, int &sh) {
+            const int k0 = JS_ROWS * st, k1 = k0 + JS_ROWS < nmo ? k0 + JS_ROWS : nmo;
+            const int nel = tri32(k1) - tri32(k0);
+            sh = (colpar + tri32(k0)) & 1;
+            cnt = (nel + sh + 1) & ~1;
+            cntw = (nel + 1) & ~1; // weight rows: T(16 st) is even and dpk is padded
+        };
+        int off = 0, v = 0;
+        unsigned n = 0, tail = 0;  // stage counters: next to issue, oldest not known to be released
+        int t_off = 0, t_v = 0, t_st = 0; // replay of the placement for stage `tail`
+        int64_t t_r = blockIdx.x;
+        int rel = 0;
         for (int64_t r = blockIdx.x; r < p.npair; r += gridDim.x) {
             const double *col = p.G + p.ldg * r;
+            const int colpar = (int)((p.ldg * r) & 1);
             for (int st = 0; st < nst; ++st) {
-                mbar_wait(&empty[s], phase ^ 1);
-                const int k0 = srow[st], k1 = srow[st + 1];
-                const int n = tri32(k1) - tri32(k0);
-                const double *src = col + tri32(k0);
-                const int sh = (int)((reinterpret_cast<uintptr_t>(src) >> 3) & 1);
+                int cnt, cntw, sh;
+                stage_size(st, colpar, cnt, cntw, sh);
+                const int sz = cnt + cntw;
+                if (off + sz > cap) { // the consumers take the same decision
+                    v += cap - off;
+                    off = 0;
+                }
+                const int beg = off;
+                off += sz;
+                v += sz;
+                while (v - rel > cap || n - tail >= JS_NB) {
+                    mbar_wait(&empty[tail % JS_NB], (tail / JS_NB) & 1);
+                    int c2, w2, s2;
+                    stage_size(t_st, (int)((p.ldg * t_r) & 1), c2, w2, s2);
+                    if (t_off + c2 + w2 > cap) {
+                        t_v += cap - t_off;
+                        t_off = 0;
+                    }
+                    t_off += c2 + w2;
+                    t_v += c2 + w2;
+                    rel = t_v;
+                    if (++t_st == nst) {
+                        t_st = 0;
+                        t_r += gridDim.x;
+                    }
+                    ++tail;
+                }
+                const int b = n % JS_NB;
+                const double *src = col + JS_ROWS * st * (JS_ROWS * st + 1) / 2;
                 const double *srcA = src - sh; // 16-byte aligned
-                int cnt = (n + sh + 1) & ~1;
-                double *dst = ringbuf + (size_t)s * p.stage_doubles;
-                if (srcA + cnt > Gend) { // the pad element would lie behind the matrix: copy the last one by hand
-                    cnt -= 2;
-                    dst[cnt] = srcA[cnt];
+                double *dst = ringbuf + beg;
+                int cg = cnt;
+                if (srcA + cg > Gend) { // the pad element would lie behind the matrix: copy the last one by hand
+                    cg -= 2;
+                    dst[cg] = srcA[cg];
                 }
-                mbar_arrive_expect_tx(&full[s], cnt * 8);
-                if (cnt > 0) bulk_load(dst, srcA, cnt * 8, &full[s]);
-                if (++s == ring) {
-                    s = 0;
-                    phase ^= 1;
-                }
+                mbar_arrive_expect_tx(&full[b], (cg + cntw) * 8);
+                if (cg > 0) bulk_load(dst, srcA, cg * 8, &full[b]);
+                bulk_load(dst + cnt, p.dpk + tri32(JS_ROWS * st), cntw * 8, &full[b]);
+                ++n;
             }
         }
         return;
@@ -159,7 +204,8 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
     }
     consumer_barrier();
 
-    int s = 0, phase = 0, held = -1;
+    int off = 0;
+    unsigned nctr = 0;
     while (r < p.npair) {
         const double2 *xc = x2 + par * NMOP;
         double xi[QL], xj[QL], bi[QL], bj[QL];
@@ -173,76 +219,15 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
         double jw = 0.0;
         const int colpar = (int)((p.ldg * r) & 1); // G is 16-byte aligned (checked by the launcher)
 
-        // Stage ST holds the packed rows [32 ST, min(32 ST + 32, nmo)): every row of it has ST blocks of 32 columns
-        // strictly left of the diagonal and ONE block that contains it, so the block structure is a compile-time
-        // property of the stage and the loop below unrolls without a data-dependent branch per block.
-        // Row pairs of this warp in a stage: A = (32 ST + 2 warp, +1), B = A + 16.
-        // weights of a row pair: w[q] = dpk[T(k) + lane + 32 q] for lane + 32 q <= k, else 0
-        auto load_w = [&](auto nf_c, auto full_c, int ka, bool hasb_, double (&wa)[QL], double (&wb)[QL]) {
-            constexpr int NF = decltype(nf_c)::value;
-            const bool hasb = decltype(full_c)::value ? true : hasb_; // every stage but the last holds 32 rows
-            const double *da = p.dpk + tri32(ka) + lane;
-            const double *db = da + ka + 1;
-            const int l = lane + 32 * NF;
-#pragma unroll
-            for (int q = 0; q < NF; ++q) wa[q] = __ldg(da + 32 * q);
-            wa[NF] = (l <= ka) ? __ldg(da + 32 * NF) : 0.0;
-            if (hasb) {
-#pragma unroll
-                for (int q = 0; q < NF; ++q) wb[q] = __ldg(db + 32 * q);
-                wb[NF] = (l <= ka + 1) ? __ldg(db + 32 * NF) : 0.0;
-            } else {
-#pragma unroll
-                for (int q = 0; q <= NF; ++q) wb[q] = 0.0;
-            }
-        };
-        // one row pair (ka, ka + 1) of a stage with NF full blocks; `base` + T(k) + l addresses P[T(k) + l]
-        auto pair = [&](auto nf_c, auto full_c, int ka, bool hasb_, const double *base, const double (&wa)[QL],
-                        const double (&wb)[QL]) {
-            constexpr int NF = decltype(nf_c)::value;
-            const bool hasb = decltype(full_c)::value ? true : hasb_;
-            const double *rowa = base + tri32(ka) + lane;
-            const double *rowb = hasb ? rowa + ka + 1 : rowa; // a missing row b re-reads row a against zero weights
-            const int kb = hasb ? ka + 1 : ka;
-            const double2 xka = xc[ka];
-            const double2 xkb = hasb ? xc[kb] : make_double2(0.0, 0.0);
-            double pia = 0.0, pja = 0.0, pib = 0.0, pjb = 0.0, jw2 = 0.0;
-#pragma unroll
-            for (int q = 0; q < NF; ++q) {
-                const double ga = rowa[32 * q], gb = rowb[32 * q];
-                pia = fma(ga, xi[q], pia);
-                pja = fma(ga, xj[q], pja);
-                pib = fma(gb, xi[q], pib);
-                pjb = fma(gb, xj[q], pjb);
-                jw = fma(ga, wa[q], jw);
-                jw2 = fma(gb, wb[q], jw2);
-                bi[q] = fma(ga, xka.x, bi[q]);
-                bj[q] = fma(ga, xka.y, bj[q]);
-                bi[q] = fma(gb, xkb.x, bi[q]);
-                bj[q] = fma(gb, xkb.y, bj[q]);
-            }
-            {
-                const int l = lane + 32 * NF;
-                const double ga = (l <= ka) ? rowa[32 * NF] : 0.0;
-                const double gb = (l <= kb) ? rowb[32 * NF] : 0.0;
-                const double gat = (l < ka) ? ga : 0.0; // the diagonal element belongs to the row sum only
-                const double gbt = (l < kb) ? gb : 0.0;
-                pia = fma(ga, xi[NF], pia);
-                pja = fma(ga, xj[NF], pja);
-                pib = fma(gb, xi[NF], pib);
-                pjb = fma(gb, xj[NF], pjb);
-                jw = fma(ga, wa[NF], jw);
-                jw2 = fma(gb, wb[NF], jw2);
-                bi[NF] = fma(gat, xka.x, bi[NF]);
-                bj[NF] = fma(gat, xka.y, bj[NF]);
-                bi[NF] = fma(gbt, xkb.x, bi[NF]);
-                bj[NF] = fma(gbt, xkb.y, bj[NF]);
-            }
-            jw += jw2;
-            // 4-value butterfly: lanes 0-7 end with sum pia, 8-15 pja, 16-23 pib, 24-31 pjb
+        // row sums of the previous pair, reduced over the lanes while the next pair's FMAs are in flight
+        double dpia = 0.0, dpja = 0.0, dpib = 0.0, dpjb = 0.0;
+        int dka = -1;
+        bool dhasb = false;
+        // 4-value butterfly: lanes 0-7 end with sum pia, 8-15 pja, 16-23 pib, 24-31 pjb
+        auto flush = [&]() {
             const bool hi = lane & 16;
-            double k0v = hi ? pib : pia, k1v = hi ? pjb : pja;
-            const double s0 = hi ? pia : pib, s1 = hi ? pja : pjb;
+            double k0v = hi ? dpib : dpia, k1v = hi ? dpjb : dpja;
+            const double s0 = hi ? dpia : dpib, s1 = hi ? dpja : dpjb;
             k0v += __shfl_xor_sync(0xffffffffu, s0, 16);
             k1v += __shfl_xor_sync(0xffffffffu, s1, 16);
             const bool b8 = lane & 8;
@@ -252,45 +237,99 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
             kv += __shfl_xor_sync(0xffffffffu, kv, 4);
             kv += __shfl_xor_sync(0xffffffffu, kv, 2);
             kv += __shfl_xor_sync(0xffffffffu, kv, 1);
-            if ((lane & 7) == 0 && (hasb || !hi)) {
-                double *dst = reinterpret_cast<double *>(va2 + (hi ? kb : ka)) + (b8 ? 1 : 0);
+            if (dka >= 0 && (lane & 7) == 0 && (dhasb || !hi)) {
+                double *dst = reinterpret_cast<double *>(va2 + (hi ? dka + 1 : dka)) + (b8 ? 1 : 0);
                 *dst = kv;
             }
         };
-        double w0a[QL], w0b[QL], w1a[QL], w1b[QL];
-        {
-            constexpr bool F0 = QL > 1;
-            if (F0 || 2 * warp < nmo)
-                load_w(std::integral_constant<int, 0>{}, std::bool_constant<F0>{}, 2 * warp, 2 * warp + 1 < nmo, w0a, w0b);
-        }
-        static_for<0, QL>([&](auto st_c) {
-            constexpr int ST = decltype(st_c)::value;
-            constexpr bool FULL = ST + 1 < QL; // all 32 rows exist
-            std::bool_constant<FULL> full_c;
-            const int kend = FULL ? 32 * ST + 32 : nmo;
-            const int kaA = 32 * ST + 2 * warp, kaB = kaA + 16;
-            if (FULL || kaB < kend) load_w(st_c, full_c, kaB, kaB + 1 < kend, w1a, w1b);
-            mbar_wait(&full[s], phase);
-            if (held >= 0) {
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&empty[held]);
+
+        static_for<0, NSTAGE>([&](auto st_c) {
+            constexpr int S = decltype(st_c)::value;
+            constexpr int NF = S / 2;
+            constexpr bool FULL = S + 2 < NSTAGE;  // all 16 rows exist
+            constexpr bool EXISTS = S + 1 < NSTAGE; // the stage exists for every nmo of this QL
+            if (EXISTS || S < nst) {
+                const int kend = (FULL || JS_ROWS * S + JS_ROWS < nmo) ? JS_ROWS * S + JS_ROWS : nmo;
+                const int ka = JS_ROWS * S + 2 * warp;
+                const int nel = tri32(kend) - tri32(JS_ROWS * S);
+                const int sh = (colpar + tri32(JS_ROWS * S)) & 1;
+                const int cnt = (nel + sh + 1) & ~1, cntw = (nel + 1) & ~1;
+                if (off + cnt + cntw > cap) off = 0; // same placement rule as the producer
+                const double *gbase = ringbuf + off - tri32(JS_ROWS * S);
+                off += cnt + cntw;
+                const int b = nctr % JS_NB;
+                mbar_wait(&full[b], (nctr / JS_NB) & 1);
+                ++nctr;
+                if (FULL || ka < kend) {
+                    const bool hasb = FULL ? true : ka + 1 < kend;
+                    const int kb = hasb ? ka + 1 : ka;
+                    const double *rowa = gbase + sh + tri32(ka) + lane;
+                    const double *rowb = hasb ? rowa + ka + 1 : rowa; // a missing row b re-reads row a against zeros
+                    const double *wra = gbase + cnt + tri32(ka) + lane;
+                    const double *wrb = hasb ? wra + ka + 1 : wra;
+                    const double2 xka = xc[ka];
+                    const double2 xkb = hasb ? xc[kb] : make_double2(0.0, 0.0);
+                    const double bscale = hasb ? 1.0 : 0.0;
+                    double pia[2] = {0.0, 0.0}, pja[2] = {0.0, 0.0}, pib[2] = {0.0, 0.0}, pjb[2] = {0.0, 0.0};
+                    double jwa = 0.0, jwb = 0.0;
+#pragma unroll
+                    for (int q = 0; q < NF; ++q) {
+                        const double ga = rowa[32 * q], gb = rowb[32 * q];
+                        const double wa = wra[32 * q], wb = wrb[32 * q];
+                        pia[q & 1] = fma(ga, xi[q], pia[q & 1]);
+                        pja[q & 1] = fma(ga, xj[q], pja[q & 1]);
+                        pib[q & 1] = fma(gb, xi[q], pib[q & 1]);
+                        pjb[q & 1] = fma(gb, xj[q], pjb[q & 1]);
+                        jwa = fma(ga, wa, jwa);
+                        jwb = fma(gb, wb, jwb);
+                        bi[q] = fma(ga, xka.x, bi[q]);
+                        bj[q] = fma(ga, xka.y, bj[q]);
+                        bi[q] = fma(gb, xkb.x, bi[q]);
+                        bj[q] = fma(gb, xkb.y, bj[q]);
+                    }
+                    {
+                        const int l = lane + 32 * NF;
+                        const double ga = (l <= ka) ? rowa[32 * NF] : 0.0;
+                        const double gb = (l <= kb) ? rowb[32 * NF] : 0.0;
+                        const double wa = (l <= ka) ? wra[32 * NF] : 0.0;
+                        const double wb = (l <= kb) ? wrb[32 * NF] : 0.0;
+                        const double gat = (l < ka) ? ga : 0.0; // the diagonal element belongs to the row sum only
+                        const double gbt = (l < kb) ? gb : 0.0;
+                        pia[NF & 1] = fma(ga, xi[NF], pia[NF & 1]);
+                        pja[NF & 1] = fma(ga, xj[NF], pja[NF & 1]);
+                        pib[NF & 1] = fma(gb, xi[NF], pib[NF & 1]);
+                        pjb[NF & 1] = fma(gb, xj[NF], pjb[NF & 1]);
+                        jwa = fma(ga, wa, jwa);
+                        jwb = fma(gb, wb, jwb);
+                        bi[NF] = fma(gat, xka.x, bi[NF]);
+                        bj[NF] = fma(gat, xka.y, bj[NF]);
+                        bi[NF] = fma(gbt, xkb.x, bi[NF]);
+                        bj[NF] = fma(gbt, xkb.y, bj[NF]);
+                    }
+                    flush(); // previous pair
+                    jw += fma(jwb, bscale, jwa);
+                    dpia = pia[0] + pia[1];
+                    dpja = pja[0] + pja[1];
+                    dpib = pib[0] + pib[1];
+                    dpjb = pjb[0] + pjb[1];
+                    dka = ka;
+                    dhasb = hasb;
+                    // Release the stage: lane 0 stores a value that depends on every shared-memory read of the stage
+                    // (row sums <- all G loads, J sums <- all weight loads), so the store cannot issue before the
+                    // last read has returned, and arrives behind it.  (An arrive placed directly behind the loads is
+                    // issued before they complete, see k3_gram.cu; deferring it to the next stage keeps two stages
+                    // per SM out of flight.)
+                    const double proof = (dpia + dpib) + (jwa + jwb);
+                    if (lane == 0) {
+                        prf[warp] = proof;
+                        mbar_arrive(&empty[b]);
+                    }
+                } else if (lane == 0) {
+                    mbar_arrive(&empty[b]); // no rows of this warp in the stage
+                }
             }
-            held = s;
-            const int sh = (colpar + tri32(32 * ST)) & 1;
-            const double *base = ringbuf + (size_t)s * p.stage_doubles + sh - tri32(32 * ST);
-            if (++s == ring) {
-                s = 0;
-                phase ^= 1;
-            }
-            if (FULL || kaA < kend) pair(st_c, full_c, kaA, kaA + 1 < kend, base, w0a, w0b);
-            if constexpr (ST + 1 < QL) {
-                constexpr bool NFULL = ST + 2 < QL;
-                const int kn = 32 * (ST + 1) + 2 * warp;
-                if (NFULL || kn < nmo)
-                    load_w(std::integral_constant<int, ST + 1>{}, std::bool_constant<NFULL>{}, kn, kn + 1 < nmo, w0a, w0b);
-            }
-            if (FULL || kaB < kend) pair(st_c, full_c, kaB, kaB + 1 < kend, base, w1a, w1b);
         });
+        flush();
 
         // ---- end of column
         const int64_t rn = r + gridDim.x;
@@ -306,9 +345,6 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) jw += __shfl_xor_sync(0xffffffffu, jw, o);
         if (lane == 0) jws[warp] = jw;
-        __syncwarp();
-        if (held >= 0 && lane == 0) mbar_arrive(&empty[held]); // every read of the column's last stage is behind us
-        held = -1;
         consumer_barrier();
         if (tid < nmo) {
             double2 v = va2[tid];
@@ -348,33 +384,28 @@ cudaError_t launch_stream_q(const JkParams &p, int smem, int num_sms, cudaStream
 
 int jk_stream_max_nmo() { return 256; }
 
-// Stage table for one column: blocks of `rows` whole packed rows (rows = 32, or 16 when three stages of 32 do not fit).
-// Returns the number of stages; fills srow[0..nst], the ring depth and the slot size in doubles.
+// Stages of one column: blocks of JS_ROWS whole packed rows and their J weights, placed back to back in a ring of
+// `stage_doubles` doubles (all the shared memory left: the bytes in flight per SM bound the HBM throughput).
+// Returns the number of stages (0: does not fit); fills srow[0..nst], ring (= stages that fit at least) and the sizes.
 int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_bytes)
 {
     const int QL = (nmo + 31) / 32, nmoP = 32 * QL;
-    const int fixed = (JS_NW + 3) * nmoP * 16 + JS_NW * 8 + (JS_MAX_STAGES + 2) * 4 + 2 * JS_MAX_RING * 8 + 64;
-    const int budget = 227 * 1024 - fixed;
-    for (int rows = 32; rows >= 32; rows /= 2) { // the consumers' stage structure is compiled in: 32 rows
-        int nst = 0, biggest = 0;
-        srow[0] = 0;
-        for (int k = 0; k < nmo; k += rows) {
-            const int k1 = k + rows < nmo ? k + rows : nmo;
-            const int n = k1 * (k1 + 1) / 2 - k * (k + 1) / 2;
-            biggest = n > biggest ? n : biggest;
-            srow[++nst] = k1;
-        }
-        const int slot = (biggest + 2 + 1) & ~1; // + alignment shift / pad element, even
-        int depth = budget / (slot * 8);
-        if (depth > JS_MAX_RING) depth = JS_MAX_RING;
-        if (depth >= 3 && nst <= JS_MAX_STAGES) {
-            *ring = depth;
-            *stage_doubles = slot;
-            *smem_bytes = depth * slot * 8 + fixed;
-            return nst;
-        }
+    const int fixed = (JS_NW + 3) * nmoP * 16 + 2 * JS_NW * 8 + 2 * JS_NB * 8 + 64;
+    const int cap = ((227 * 1024 - fixed) / 8) & ~1;
+    int nst = 0, biggest = 0;
+    srow[0] = 0;
+    for (int k = 0; k < nmo; k += JS_ROWS) { // the consumers' stage structure is compiled in: JS_ROWS rows per stage
+        const int k1 = k + JS_ROWS < nmo ? k + JS_ROWS : nmo;
+        const int n = k1 * (k1 + 1) / 2 - k * (k + 1) / 2;
+        biggest = n > biggest ? n : biggest;
+        srow[++nst] = k1;
     }
-    return 0;
+    const int slot = 2 * ((biggest + 2 + 1) & ~1); // G rows (+ alignment shift / pad element) | weight rows
+    if (cap / slot < 3 || nst > JS_MAX_STAGES) return 0;
+    *ring = cap / slot;
+    *stage_doubles = cap;
+    *smem_bytes = cap * 8 + fixed;
+    return nst;
 }
 
 cudaError_t launch_jk_stream(const JkParams &p, int smem, int num_sms, cudaStream_t s)
