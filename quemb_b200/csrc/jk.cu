@@ -202,22 +202,35 @@ __global__ void __launch_bounds__(512, 1) jk_rows_kernel(JkParams p)
     }
 }
 
-// K[a,k] = sum_{j<=a} R1[(a,j)][k] + sum_{i>a} R2[(i,a)][k]   (fixed order);   J[a,k] = sum_w Jp[T(max)+min][w]
-__global__ void jk_reduce_kernel(JkParams p, double *__restrict__ J, double *__restrict__ K, int64_t ldo)
+// K[a,k] = sum_{j<=a} R1[(a,j)][k] + sum_{i>a} R2[(i,a)][k];   J[a,k] = sum_w Jp[T(max)+min][w]
+// The nmo terms of K[a,k] are dealt to JR_PARTS threads (term t -> part t mod JR_PARTS), each sums its terms in
+// order, the parts are added in order: fixed summation order, JR_PARTS times the loads in flight.
+constexpr int JR_KX = 32, JR_PARTS = 8;
+__global__ void __launch_bounds__(JR_KX *JR_PARTS) jk_reduce_kernel(JkParams p, double *__restrict__ J, double *__restrict__ K, int64_t ldo)
 {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ double part_s[JR_PARTS][JR_KX];
+    const int kx = threadIdx.x % JR_KX, part = threadIdx.x / JR_KX;
+    const int k = blockIdx.x * JR_KX + kx;
     const int a = blockIdx.y;
     const int nmo = p.nmo;
-    if (k >= nmo) return;
     double s = 0.0;
-    for (int j = 0; j <= a; ++j) s += p.R1[(tri(a) + j) * nmo + k];
-    for (int i = a + 1; i < nmo; ++i) s += p.R2[(tri(i) + a) * nmo + k];
-    K[a + ldo * k] = s;
-    const int hi = a > k ? a : k, lo = a > k ? k : a;
-    const double *jp = p.Jp + (tri(hi) + lo) * p.njp;
-    double t = 0.0;
-    for (int w = 0; w < p.njp; ++w) t += jp[w];
-    J[a + ldo * k] = t;
+    if (k < nmo) {
+        for (int t = part; t < nmo; t += JR_PARTS)
+            s += t <= a ? p.R1[(tri(a) + t) * nmo + k] : p.R2[(tri(t) + a) * nmo + k];
+    }
+    part_s[part][kx] = s;
+    __syncthreads();
+    if (part == 0 && k < nmo) {
+        double t = part_s[0][kx];
+#pragma unroll
+        for (int q = 1; q < JR_PARTS; ++q) t += part_s[q][kx];
+        K[a + ldo * k] = t;
+        const int hi = a > k ? a : k, lo = a > k ? k : a;
+        const double *jp = p.Jp + (tri(hi) + lo) * p.njp;
+        double u = 0.0;
+        for (int w = 0; w < p.njp; ++w) u += jp[w];
+        J[a + ldo * k] = u;
+    }
 }
 
 int jk_warps() { return JK_MAXWARPS; }
@@ -254,8 +267,8 @@ cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int 
 
 cudaError_t launch_jk_reduce(const JkParams &p, double *J, double *K, int64_t ldo, cudaStream_t s)
 {
-    dim3 g2((p.nmo + 127) / 128, p.nmo);
-    jk_reduce_kernel<<<g2, 128, 0, s>>>(p, J, K, ldo);
+    dim3 g2((p.nmo + JR_KX - 1) / JR_KX, p.nmo);
+    jk_reduce_kernel<<<g2, JR_KX * JR_PARTS, 0, s>>>(p, J, K, ldo);
     return cudaGetLastError();
 }
 

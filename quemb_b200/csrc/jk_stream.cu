@@ -108,8 +108,8 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
     double2 *x2 = slab + JS_NW * NMOP;
     double2 *va2 = x2 + 2 * NMOP;
     double *jws = reinterpret_cast<double *>(va2 + NMOP);
-    double *prf = jws + JS_NW; // per-warp sink of the release proofs
-    uint64_t *full = reinterpret_cast<uint64_t *>(prf + JS_NW);
+    int *prf = reinterpret_cast<int *>(jws + JS_NW); // per-warp sink of the release proofs
+    uint64_t *full = reinterpret_cast<uint64_t *>(prf + 2 * JS_NW);
     uint64_t *empty = full + JS_NB;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                     const double2 xkb = hasb ? xc[kb] : make_double2(0.0, 0.0);
                     const double bscale = hasb ? 1.0 : 0.0;
                     double pia[2] = {0.0, 0.0}, pja[2] = {0.0, 0.0}, pib[2] = {0.0, 0.0}, pjb[2] = {0.0, 0.0};
-                    double jwa = 0.0, jwb = 0.0;
+                    double jwa[2] = {0.0, 0.0}, jwb[2] = {0.0, 0.0};
 #pragma unroll
                     for (int q = 0; q < NF; ++q) {
                         const double ga = rowa[32 * q], gb = rowb[32 * q];
@@ -280,8 +280,8 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                         pja[q & 1] = fma(ga, xj[q], pja[q & 1]);
                         pib[q & 1] = fma(gb, xi[q], pib[q & 1]);
                         pjb[q & 1] = fma(gb, xj[q], pjb[q & 1]);
-                        jwa = fma(ga, wa, jwa);
-                        jwb = fma(gb, wb, jwb);
+                        jwa[q & 1] = fma(ga, wa, jwa[q & 1]);
+                        jwb[q & 1] = fma(gb, wb, jwb[q & 1]);
                         bi[q] = fma(ga, xka.x, bi[q]);
                         bj[q] = fma(ga, xka.y, bj[q]);
                         bi[q] = fma(gb, xkb.x, bi[q]);
@@ -299,15 +299,15 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                         pja[NF & 1] = fma(ga, xj[NF], pja[NF & 1]);
                         pib[NF & 1] = fma(gb, xi[NF], pib[NF & 1]);
                         pjb[NF & 1] = fma(gb, xj[NF], pjb[NF & 1]);
-                        jwa = fma(ga, wa, jwa);
-                        jwb = fma(gb, wb, jwb);
+                        jwa[NF & 1] = fma(ga, wa, jwa[NF & 1]);
+                        jwb[NF & 1] = fma(gb, wb, jwb[NF & 1]);
                         bi[NF] = fma(gat, xka.x, bi[NF]);
                         bj[NF] = fma(gat, xka.y, bj[NF]);
                         bi[NF] = fma(gbt, xkb.x, bi[NF]);
                         bj[NF] = fma(gbt, xkb.y, bj[NF]);
                     }
                     flush(); // previous pair
-                    jw += fma(jwb, bscale, jwa);
+                    jw += fma(jwb[0] + jwb[1], bscale, jwa[0] + jwa[1]);
                     dpia = pia[0] + pia[1];
                     dpja = pja[0] + pja[1];
                     dpib = pib[0] + pib[1];
@@ -315,11 +315,13 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                     dka = ka;
                     dhasb = hasb;
                     // Release the stage: lane 0 stores a value that depends on every shared-memory read of the stage
-                    // (row sums <- all G loads, J sums <- all weight loads), so the store cannot issue before the
+                    // (a few bits of the row sums <- all G loads and of the J sums <- all weight loads), so the store cannot issue before the
                     // last read has returned, and arrives behind it.  (An arrive placed directly behind the loads is
                     // issued before they complete, see k3_gram.cu; deferring it to the next stage keeps two stages
                     // per SM out of flight.)
-                    const double proof = (dpia + dpib) + (jwa + jwb);
+                    const int proof = (__double2loint(pia[0]) ^ __double2loint(pia[1]) ^ __double2loint(pib[0])) ^
+                                      (__double2loint(pib[1]) ^ __double2loint(jwa[0]) ^ __double2loint(jwa[1])) ^
+                                      (__double2loint(jwb[0]) ^ __double2loint(jwb[1]));
                     if (lane == 0) {
                         prf[warp] = proof;
                         mbar_arrive(&empty[b]);
