@@ -380,6 +380,35 @@ def test_jk_multi_chunk_matches_torch(q, jk_kernel):
     assert np.abs(vk - vk_ref).max() <= 1e-10 * max(1.0, np.abs(vk_ref).max())
 
 
+def test_jk_stream_kernel_all_block_structures(q, monkeypatch):
+    """jk_stream.cu compiles the block structure of every 16-row stage in (QL = ceil(nmo / 32) variants, partial
+    last stages, a lone last row): fragment sizes around every boundary, the streaming kernel against the chunked
+    kernel (itself checked against torch / the oracle above), bitwise repeatable over many launches (a stage
+    released before its reads returned would show up here), and the fallback above 256 orbitals."""
+    p = syn.make_chain_problem(n_units=14, ao_per_unit=24, n_end=5, naux=96, frag_halfwidth=2, n_bath=60,
+                               sigma=0.94, seed=311, n_frag=8)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    T.whiten(p.L_PQ)
+    rng = np.random.default_rng(17)
+    for nmo in (1, 2, 15, 16, 17, 31, 32, 33, 48, 63, 65, 97, 128, 129, 161, 176, 177, 201, 224, 225, 255, 256, 260):
+        TA = np.linalg.qr(rng.standard_normal((p.nao, nmo)))[0]
+        ws = q.transform_integral_resident(T, TA, p.S_abs, None, 0.0)
+        D = rng.standard_normal((nmo, nmo))
+        D = D + D.T
+        monkeypatch.setenv("QEMB_JK_KERNEL", "stream")
+        vj, vk = ws.jk(D)
+        reps = 40 if nmo in (33, 201, 256) else 2
+        for _ in range(reps):
+            vj2, vk2 = ws.jk(D)
+            assert np.array_equal(vj, vj2) and np.array_equal(vk, vk2), nmo
+        monkeypatch.setenv("QEMB_JK_KERNEL", "rows")
+        vj_r, vk_r = ws.jk(D)
+        sj, sk = max(1.0, np.abs(vj_r).max()), max(1.0, np.abs(vk_r).max())
+        assert np.abs(vj - vj_r).max() <= 1e-12 * sj and np.abs(vk - vk_r).max() <= 1e-12 * sk, nmo
+        if nmo > 256:
+            assert np.array_equal(vj, vj_r)  # both calls ran the chunked kernel
+
+
 def test_dense_int_direct_DF_on_the_same_kernels(q):
     """the unscreened limit against a numpy restatement of integral_direct_DF
     (eri_onthefly.py:127-145)."""
