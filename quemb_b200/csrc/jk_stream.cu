@@ -35,11 +35,20 @@ __device__ __forceinline__ void static_for(F &&f)
         static_for<I + 1, N>(f);
     }
 }
-constexpr int JS_NW = 8;                      // consumer warps
+#ifndef JS_NW_DEF
+#define JS_NW_DEF 8
+#endif
+#ifndef JS_ROWS_DEF
+#define JS_ROWS_DEF 16
+#endif
+constexpr int JS_NW = JS_NW_DEF;              // consumer warps
 constexpr int JS_THREADS = 32 * (JS_NW + 1);  // + producer warp
 constexpr int JS_NB = 16;                     // mbarrier pairs = stages in flight at most
 constexpr int JS_MAX_STAGES = 40;             // stages per column (<= 2 * 8)
-constexpr int JS_ROWS = 16;                   // packed rows per stage: one row pair per consumer warp
+constexpr int JS_ROWS = JS_ROWS_DEF;          // packed rows per stage (8 or 16): one row pair per warp of a group
+constexpr int JS_PAIRS = JS_ROWS / 2;         // warps per group
+constexpr int JS_GROUPS = JS_NW / JS_PAIRS;   // stage S is processed by group S mod JS_GROUPS
+static_assert(JS_NW % JS_PAIRS == 0 && 32 % JS_ROWS == 0, "warp groups / block structure");
 
 __device__ __forceinline__ int tri32(int k) { return (k * (k + 1)) >> 1; }
 
@@ -93,14 +102,14 @@ __device__ __forceinline__ void pair_of(int64_t r, int &i, int &j)
 // shared memory: ring of stage_doubles doubles, a stage = [G rows | weight rows] placed back to back (wrapping to 0
 //                when the next one does not fit) | slab[JS_NW][nmoP] double2 | x2[2][nmoP] double2 | va2[nmoP] double2 |
 //                jws[JS_NW] | full[JS_NB], empty[JS_NB]
-// Stage S = packed rows [16 S, min(16 S + 16, nmo)): warp w owns the row pair (16 S + 2 w, + 1).  Every row of the stage
-// has NF = S / 2 blocks of 32 columns strictly left of the diagonal and one block that contains it, so the block
+// Stage S = packed rows [R S, min(R S + R, nmo)), R = JS_ROWS, processed by warp group S mod JS_GROUPS: warp pw of the group
+// owns the row pair (R S + 2 pw, + 1).  Every row of the stage has NF = R S / 32 blocks of 32 columns strictly left of the diagonal and one block that contains it, so the block
 // structure is a compile-time property of the stage and the stage loop unrolls without data-dependent branches.
 template <int QL>
 __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
 {
     constexpr int NMOP = 32 * QL;
-    constexpr int NSTAGE = 2 * QL; // stages 0 .. 2 QL - 2 always exist (nmo > 32 (QL - 1)), the last one may not
+    constexpr int NSTAGE = (32 / JS_ROWS) * QL; // stages up to row 32 (QL - 1) always exist (nmo > 32 (QL - 1))
     extern __shared__ __align__(16) double js_smem[];
     const int cap = p.stage_doubles; // ring capacity in doubles (even); stages are placed back to back
     double *ringbuf = js_smem;
@@ -109,16 +118,23 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
     double2 *va2 = x2 + 2 * NMOP;
     double *jws = reinterpret_cast<double *>(va2 + NMOP);
     int *prf = reinterpret_cast<int *>(jws + JS_NW); // per-warp sink of the release proofs
-    uint64_t *full = reinterpret_cast<uint64_t *>(prf + 2 * JS_NW);
+    int *stab = prf + 2 * JS_NW; // per stage: elements, T(first row)
+    uint64_t *full = reinterpret_cast<uint64_t *>(stab + 2 * JS_MAX_STAGES);
     uint64_t *empty = full + JS_NB;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int group = warp / JS_PAIRS, pw = warp % JS_PAIRS;
     const int nmo = p.nmo, nst = p.nstages;
 
+    for (int st = tid; st < nst; st += JS_THREADS) {
+        const int k0 = JS_ROWS * st, k1 = k0 + JS_ROWS < nmo ? k0 + JS_ROWS : nmo;
+        stab[2 * st] = tri32(k1) - tri32(k0);
+        stab[2 * st + 1] = tri32(k0);
+    }
     if (tid == 0) {
         for (int s = 0; s < JS_NB; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], JS_NW);
+            mbar_init(&empty[s], JS_PAIRS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -132,24 +148,21 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
         // a wrap), `rel` is v at the end of the last stage known to be released.  Stages are released in order, so a
         // region is free as soon as (its end in v) - rel <= cap.  The released stages' ends are replayed with the same
         // placement rule instead of being stored.
-        auto stage_size = [&](int st, int colpar, int &cnt, int &cntw, int &sh) {
-            const int k0 = JS_ROWS * st, k1 = k0 + JS_ROWS < nmo ? k0 + JS_ROWS : nmo;
-            const int nel = tri32(k1) - tri32(k0);
-            sh = (colpar + tri32(k0)) & 1;
-            cnt = (nel + sh + 1) & ~1;
-            cntw = (nel + 1) & ~1; // weight rows: T(16 st) is even and dpk is padded
-        };
+        // (T(JS_ROWS st) is even, so the alignment shift of a stage is the parity of the column start.)
         int off = 0, v = 0;
         unsigned n = 0, tail = 0;  // stage counters: next to issue, oldest not known to be released
         int t_off = 0, t_v = 0, t_st = 0; // replay of the placement for stage `tail`
-        int64_t t_r = blockIdx.x;
         int rel = 0;
-        for (int64_t r = blockIdx.x; r < p.npair; r += gridDim.x) {
-            const double *col = p.G + p.ldg * r;
-            const int colpar = (int)((p.ldg * r) & 1);
+        const int dpar = (int)((p.ldg * gridDim.x) & 1); // parity step from one of my columns to the next
+        int colpar = (int)((p.ldg * blockIdx.x) & 1), t_colpar = colpar;
+        const int64_t colstep = p.ldg * gridDim.x;
+        const double *col = p.G + p.ldg * blockIdx.x;
+        for (int64_t r = blockIdx.x; r < p.npair; r += gridDim.x, col += colstep, colpar ^= dpar) {
             for (int st = 0; st < nst; ++st) {
-                int cnt, cntw, sh;
-                stage_size(st, colpar, cnt, cntw, sh);
+                const int nel = stab[2 * st], tr = stab[2 * st + 1];
+                const int sh = colpar;
+                const int cnt = (nel + sh + 1) & ~1;
+                const int cntw = (nel + 1) & ~1; // weight rows: dpk is aligned and padded
                 const int sz = cnt + cntw;
                 if (off + sz > cap) { // the consumers take the same decision
                     v += cap - off;
@@ -160,24 +173,23 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 v += sz;
                 while (v - rel > cap || n - tail >= JS_NB) {
                     mbar_wait(&empty[tail % JS_NB], (tail / JS_NB) & 1);
-                    int c2, w2, s2;
-                    stage_size(t_st, (int)((p.ldg * t_r) & 1), c2, w2, s2);
-                    if (t_off + c2 + w2 > cap) {
+                    const int nel2 = stab[2 * t_st];
+                    const int sz2 = ((nel2 + t_colpar + 1) & ~1) + ((nel2 + 1) & ~1);
+                    if (t_off + sz2 > cap) {
                         t_v += cap - t_off;
                         t_off = 0;
                     }
-                    t_off += c2 + w2;
-                    t_v += c2 + w2;
+                    t_off += sz2;
+                    t_v += sz2;
                     rel = t_v;
                     if (++t_st == nst) {
                         t_st = 0;
-                        t_r += gridDim.x;
+                        t_colpar ^= dpar;
                     }
                     ++tail;
                 }
                 const int b = n % JS_NB;
-                const double *src = col + JS_ROWS * st * (JS_ROWS * st + 1) / 2;
-                const double *srcA = src - sh; // 16-byte aligned
+                const double *srcA = col + tr - sh; // 16-byte aligned
                 double *dst = ringbuf + beg;
                 int cg = cnt;
                 if (srcA + cg > Gend) { // the pad element would lie behind the matrix: copy the last one by hand
@@ -186,7 +198,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 }
                 mbar_arrive_expect_tx(&full[b], (cg + cntw) * 8);
                 if (cg > 0) bulk_load(dst, srcA, cg * 8, &full[b]);
-                bulk_load(dst + cnt, p.dpk + tri32(JS_ROWS * st), cntw * 8, &full[b]);
+                bulk_load(dst + cnt, p.dpk + tr, cntw * 8, &full[b]);
                 ++n;
             }
         }
@@ -245,12 +257,12 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
 
         static_for<0, NSTAGE>([&](auto st_c) {
             constexpr int S = decltype(st_c)::value;
-            constexpr int NF = S / 2;
-            constexpr bool FULL = S + 2 < NSTAGE;  // all 16 rows exist
-            constexpr bool EXISTS = S + 1 < NSTAGE; // the stage exists for every nmo of this QL
+            constexpr int NF = JS_ROWS * S / 32;
+            constexpr bool FULL = JS_ROWS * (S + 1) <= 32 * (QL - 1); // all rows exist for every nmo of this QL
+            constexpr bool EXISTS = JS_ROWS * S <= 32 * (QL - 1);     // the stage exists for every nmo of this QL
             if (EXISTS || S < nst) {
                 const int kend = (FULL || JS_ROWS * S + JS_ROWS < nmo) ? JS_ROWS * S + JS_ROWS : nmo;
-                const int ka = JS_ROWS * S + 2 * warp;
+                const int ka = JS_ROWS * S + 2 * pw;
                 const int nel = tri32(kend) - tri32(JS_ROWS * S);
                 const int sh = (colpar + tri32(JS_ROWS * S)) & 1;
                 const int cnt = (nel + sh + 1) & ~1, cntw = (nel + 1) & ~1;
@@ -258,8 +270,10 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 const double *gbase = ringbuf + off - tri32(JS_ROWS * S);
                 off += cnt + cntw;
                 const int b = nctr % JS_NB;
-                mbar_wait(&full[b], (nctr / JS_NB) & 1);
+                const int par_b = (nctr / JS_NB) & 1;
                 ++nctr;
+                if (JS_GROUPS == 1 || group == S % JS_GROUPS) { // other groups only keep placement and counters in step
+                mbar_wait(&full[b], par_b);
                 if (FULL || ka < kend) {
                     const bool hasb = FULL ? true : ka + 1 < kend;
                     const int kb = hasb ? ka + 1 : ka;
@@ -329,6 +343,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 } else if (lane == 0) {
                     mbar_arrive(&empty[b]); // no rows of this warp in the stage
                 }
+                }
             }
         });
         flush();
@@ -392,7 +407,7 @@ int jk_stream_max_nmo() { return 256; }
 int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_bytes)
 {
     const int QL = (nmo + 31) / 32, nmoP = 32 * QL;
-    const int fixed = (JS_NW + 3) * nmoP * 16 + 2 * JS_NW * 8 + 2 * JS_NB * 8 + 64;
+    const int fixed = (JS_NW + 3) * nmoP * 16 + 2 * JS_NW * 8 + 2 * JS_MAX_STAGES * 4 + 2 * JS_NB * 8 + 64;
     const int cap = ((227 * 1024 - fixed) / 8) & ~1;
     int nst = 0, biggest = 0;
     srow[0] = 0;
