@@ -321,6 +321,20 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
     # one extra untimed pass that collects per-kernel event times (each fragment waited for)
     device_step(True)
     ctx.synchronize()
+    # the consumer right behind the path, informational: J/K of one density from the (ij|kl) the
+    # last fragment left on the device (HBM bound: 8 npair^2 bytes read once)
+    consumer = None
+    if rank == 0 and mine:
+        n_last = p.TAs[mine[-1]].shape[1]
+        Dm = np.random.default_rng(1).standard_normal((n_last, n_last))
+        Dm = Dm + Dm.T
+        best, nb = None, 0.0
+        for _ in range(4):
+            b.ws.jk(Dm)
+            ms_jk, nb = b.ws.jk_time()
+            best = ms_jk if best is None else min(best, ms_jk)
+        consumer = {"kernel": "jk_stream_kernel + jk_reduce_kernel (J and K of one density from the resident (ij|kl))",
+                    "fragment_nmo": int(n_last), "ms": best, "gbs": nb / best / 1e6}
 
     # ---- e2e: host buffers in, pinned host buffers out ------------------------------------------------
     d2h = sum(8 * (t.shape[1] * (t.shape[1] + 1) // 2) ** 2 for t in (p.TAs[i] for i in mine))
@@ -404,6 +418,8 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
     mp = ROOT / "MEASURED_PEAKS.json"
     if mp.exists():
         peaks = json.loads(mp.read_text())
+    if consumer and peaks.get("hbm_gbs"):
+        consumer["hbm_frac"] = consumer["gbs"] / peaks["hbm_gbs"]
     line = {
         "metric": METRIC, "value": t_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_dev * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
@@ -424,6 +440,7 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
         "per_kernel": per_kernel,
         "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
         "staging_s": staging_s,
+        "consumer": consumer,
         "cpu_baseline": cpu_baseline,
         "e2e": {"value": t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
                 "result_bytes_per_step": int(d2h_result_all), "wall_s": wall_e2e, "steps": e2e_steps,
