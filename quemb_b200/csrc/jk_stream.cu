@@ -35,20 +35,28 @@ __device__ __forceinline__ void static_for(F &&f)
         static_for<I + 1, N>(f);
     }
 }
-#ifndef JS_NW_DEF
-#define JS_NW_DEF 8
-#endif
-#ifndef JS_ROWS_DEF
-#define JS_ROWS_DEF 16
-#endif
-constexpr int JS_NW = JS_NW_DEF;              // consumer warps
+constexpr int JS_NW = 8;                      // consumer warps: one row pair each per 16 packed rows of a stage
 constexpr int JS_THREADS = 32 * (JS_NW + 1);  // + producer warp
 constexpr int JS_NB = 16;                     // mbarrier pairs = stages in flight at most
-constexpr int JS_MAX_STAGES = 40;             // stages per column (<= 2 * 8)
-constexpr int JS_ROWS = JS_ROWS_DEF;          // packed rows per stage (8 or 16): one row pair per warp of a group
-constexpr int JS_PAIRS = JS_ROWS / 2;         // warps per group
-constexpr int JS_GROUPS = JS_NW / JS_PAIRS;   // stage S is processed by group S mod JS_GROUPS
-static_assert(JS_NW % JS_PAIRS == 0 && 32 % JS_ROWS == 0, "warp groups / block structure");
+constexpr int JS_MAX_STAGES = 16;             // stages per column
+// Stage boundaries in packed rows (multiples of 16, identical for every fragment): tall stages where the rows are
+// short -- a warp then has 4 / 2 independent row pairs between two waits -- and 16 rows from row 128 up.
+__host__ __device__ constexpr int js_row0(int S) { return S == 0 ? 0 : S == 1 ? 64 : S == 2 ? 96 : 128 + 16 * (S - 3); }
+// Stages below JS_WSM carry their J weights in the ring; from JS_WSM up the ring would hold G only (more bytes of G
+// in flight per SM) and the consumers fetch the weights of their row pair from L2 into registers before they wait
+// for the stage.  Measured at nmo 201: JS_WSM = 3 / 5 / 6 / 7 / 8 -> 1.01 / 1.16 / 1.13 / 1.10 / 1.05 ms, all stages
+// with staged weights (the default, 16 = more than there are stages) 0.92 ms: the L2 latency of the weights costs
+// more than the ring space they take.
+#ifndef JS_WSM_DEF
+#define JS_WSM_DEF 16
+#endif
+constexpr int JS_WSM = JS_WSM_DEF;
+__host__ __device__ constexpr int js_stages(int rows) // stages that cover the packed rows [0, rows)
+{
+    int S = 0;
+    while (js_row0(S) < rows) ++S;
+    return S;
+}
 
 __device__ __forceinline__ int tri32(int k) { return (k * (k + 1)) >> 1; }
 
@@ -102,14 +110,15 @@ __device__ __forceinline__ void pair_of(int64_t r, int &i, int &j)
 // shared memory: ring of stage_doubles doubles, a stage = [G rows | weight rows] placed back to back (wrapping to 0
 //                when the next one does not fit) | slab[JS_NW][nmoP] double2 | x2[2][nmoP] double2 | va2[nmoP] double2 |
 //                jws[JS_NW] | full[JS_NB], empty[JS_NB]
-// Stage S = packed rows [R S, min(R S + R, nmo)), R = JS_ROWS, processed by warp group S mod JS_GROUPS: warp pw of the group
-// owns the row pair (R S + 2 pw, + 1).  Every row of the stage has NF = R S / 32 blocks of 32 columns strictly left of the diagonal and one block that contains it, so the block
+// Stage S = packed rows [js_row0(S), min(js_row0(S + 1), nmo)); in every 16 rows of it warp w owns the row pair
+// (first row + 2 w, + 1).  A row k has NF = k / 32 blocks of 32 columns strictly left of the diagonal and one block that
+// contains it, the same NF for all the rows of a 16-row group, so the block
 // structure is a compile-time property of the stage and the stage loop unrolls without data-dependent branches.
 template <int QL>
 __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
 {
     constexpr int NMOP = 32 * QL;
-    constexpr int NSTAGE = (32 / JS_ROWS) * QL; // stages up to row 32 (QL - 1) always exist (nmo > 32 (QL - 1))
+    constexpr int NSTAGE = js_stages(32 * QL); // stages that start at or below row 32 (QL - 1) always exist
     extern __shared__ __align__(16) double js_smem[];
     const int cap = p.stage_doubles; // ring capacity in doubles (even); stages are placed back to back
     double *ringbuf = js_smem;
@@ -123,18 +132,17 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
     uint64_t *empty = full + JS_NB;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int group = warp / JS_PAIRS, pw = warp % JS_PAIRS;
     const int nmo = p.nmo, nst = p.nstages;
 
     for (int st = tid; st < nst; st += JS_THREADS) {
-        const int k0 = JS_ROWS * st, k1 = k0 + JS_ROWS < nmo ? k0 + JS_ROWS : nmo;
+        const int k0 = js_row0(st), k1 = js_row0(st + 1) < nmo ? js_row0(st + 1) : nmo;
         stab[2 * st] = tri32(k1) - tri32(k0);
         stab[2 * st + 1] = tri32(k0);
     }
     if (tid == 0) {
         for (int s = 0; s < JS_NB; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], JS_PAIRS);
+            mbar_init(&empty[s], JS_NW);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -148,7 +156,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
         // a wrap), `rel` is v at the end of the last stage known to be released.  Stages are released in order, so a
         // region is free as soon as (its end in v) - rel <= cap.  The released stages' ends are replayed with the same
         // placement rule instead of being stored.
-        // (T(JS_ROWS st) is even, so the alignment shift of a stage is the parity of the column start.)
+        // (A stage starts at a multiple of 16 rows, T of it is even: the alignment shift is the parity of the column start.)
         int off = 0, v = 0;
         unsigned n = 0, tail = 0;  // stage counters: next to issue, oldest not known to be released
         int t_off = 0, t_v = 0, t_st = 0; // replay of the placement for stage `tail`
@@ -162,7 +170,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 const int nel = stab[2 * st], tr = stab[2 * st + 1];
                 const int sh = colpar;
                 const int cnt = (nel + sh + 1) & ~1;
-                const int cntw = (nel + 1) & ~1; // weight rows: dpk is aligned and padded
+                const int cntw = st < JS_WSM ? (nel + 1) & ~1 : 0; // weight rows: dpk is aligned and padded
                 const int sz = cnt + cntw;
                 if (off + sz > cap) { // the consumers take the same decision
                     v += cap - off;
@@ -174,7 +182,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 while (v - rel > cap || n - tail >= JS_NB) {
                     mbar_wait(&empty[tail % JS_NB], (tail / JS_NB) & 1);
                     const int nel2 = stab[2 * t_st];
-                    const int sz2 = ((nel2 + t_colpar + 1) & ~1) + ((nel2 + 1) & ~1);
+                    const int sz2 = ((nel2 + t_colpar + 1) & ~1) + (t_st < JS_WSM ? (nel2 + 1) & ~1 : 0);
                     if (t_off + sz2 > cap) {
                         t_v += cap - t_off;
                         t_off = 0;
@@ -198,7 +206,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                 }
                 mbar_arrive_expect_tx(&full[b], (cg + cntw) * 8);
                 if (cg > 0) bulk_load(dst, srcA, cg * 8, &full[b]);
-                bulk_load(dst + cnt, p.dpk + tr, cntw * 8, &full[b]);
+                if (cntw > 0) bulk_load(dst + cnt, p.dpk + tr, cntw * 8, &full[b]);
                 ++n;
             }
         }
@@ -257,92 +265,126 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
 
         static_for<0, NSTAGE>([&](auto st_c) {
             constexpr int S = decltype(st_c)::value;
-            constexpr int NF = JS_ROWS * S / 32;
-            constexpr bool FULL = JS_ROWS * (S + 1) <= 32 * (QL - 1); // all rows exist for every nmo of this QL
-            constexpr bool EXISTS = JS_ROWS * S <= 32 * (QL - 1);     // the stage exists for every nmo of this QL
+            constexpr int R0 = js_row0(S), R1 = js_row0(S + 1);
+            constexpr bool FULL = R1 <= 32 * (QL - 1);   // all its rows exist for every nmo of this QL
+            constexpr bool EXISTS = R0 <= 32 * (QL - 1); // the stage exists for every nmo of this QL
             if (EXISTS || S < nst) {
-                const int kend = (FULL || JS_ROWS * S + JS_ROWS < nmo) ? JS_ROWS * S + JS_ROWS : nmo;
-                const int ka = JS_ROWS * S + 2 * pw;
-                const int nel = tri32(kend) - tri32(JS_ROWS * S);
-                const int sh = (colpar + tri32(JS_ROWS * S)) & 1;
-                const int cnt = (nel + sh + 1) & ~1, cntw = (nel + 1) & ~1;
+                const int kend = (FULL || R1 < nmo) ? R1 : nmo;
+                const int nel = FULL ? (R1 * (R1 + 1) - R0 * (R0 + 1)) / 2 : tri32(kend) - (R0 * (R0 + 1)) / 2;
+                const int sh = colpar;
+                constexpr bool WSM = S < JS_WSM; // weights in the ring; else (16-row stage, one pair) from L2
+                const int cnt = (nel + sh + 1) & ~1, cntw = WSM ? (nel + 1) & ~1 : 0;
                 if (off + cnt + cntw > cap) off = 0; // same placement rule as the producer
-                const double *gbase = ringbuf + off - tri32(JS_ROWS * S);
+                const double *gbase = ringbuf + off - (R0 * (R0 + 1)) / 2;
                 off += cnt + cntw;
-                const int b = nctr % JS_NB;
-                const int par_b = (nctr / JS_NB) & 1;
-                ++nctr;
-                if (JS_GROUPS == 1 || group == S % JS_GROUPS) { // other groups only keep placement and counters in step
-                mbar_wait(&full[b], par_b);
-                if (FULL || ka < kend) {
-                    const bool hasb = FULL ? true : ka + 1 < kend;
-                    const int kb = hasb ? ka + 1 : ka;
-                    const double *rowa = gbase + sh + tri32(ka) + lane;
-                    const double *rowb = hasb ? rowa + ka + 1 : rowa; // a missing row b re-reads row a against zeros
-                    const double *wra = gbase + cnt + tri32(ka) + lane;
-                    const double *wrb = hasb ? wra + ka + 1 : wra;
-                    const double2 xka = xc[ka];
-                    const double2 xkb = hasb ? xc[kb] : make_double2(0.0, 0.0);
-                    const double bscale = hasb ? 1.0 : 0.0;
-                    double pia[2] = {0.0, 0.0}, pja[2] = {0.0, 0.0}, pib[2] = {0.0, 0.0}, pjb[2] = {0.0, 0.0};
-                    double jwa[2] = {0.0, 0.0}, jwb[2] = {0.0, 0.0};
+                double wga[QL], wgb[QL];
+                if constexpr (!WSM) {
+                    static_assert(WSM || R1 - R0 == 16, "one row pair per warp in the stages without staged weights");
+                    constexpr int NF0 = R0 / 32;
+                    const int ka = R0 + 2 * warp;
+                    if (FULL || ka < kend) {
+                        const bool hasb = FULL ? true : ka + 1 < kend;
+                        const double *da = p.dpk + tri32(ka) + lane, *db = da + ka + 1;
+                        const int l = lane + 32 * NF0;
 #pragma unroll
-                    for (int q = 0; q < NF; ++q) {
-                        const double ga = rowa[32 * q], gb = rowb[32 * q];
-                        const double wa = wra[32 * q], wb = wrb[32 * q];
-                        pia[q & 1] = fma(ga, xi[q], pia[q & 1]);
-                        pja[q & 1] = fma(ga, xj[q], pja[q & 1]);
-                        pib[q & 1] = fma(gb, xi[q], pib[q & 1]);
-                        pjb[q & 1] = fma(gb, xj[q], pjb[q & 1]);
-                        jwa[q & 1] = fma(ga, wa, jwa[q & 1]);
-                        jwb[q & 1] = fma(gb, wb, jwb[q & 1]);
-                        bi[q] = fma(ga, xka.x, bi[q]);
-                        bj[q] = fma(ga, xka.y, bj[q]);
-                        bi[q] = fma(gb, xkb.x, bi[q]);
-                        bj[q] = fma(gb, xkb.y, bj[q]);
+                        for (int q = 0; q < NF0; ++q) {
+                            wga[q] = __ldg(da + 32 * q);
+                            wgb[q] = hasb ? __ldg(db + 32 * q) : 0.0;
+                        }
+                        wga[NF0] = (l <= ka) ? __ldg(da + 32 * NF0) : 0.0;
+                        wgb[NF0] = (hasb && l <= ka + 1) ? __ldg(db + 32 * NF0) : 0.0;
                     }
-                    {
-                        const int l = lane + 32 * NF;
-                        const double ga = (l <= ka) ? rowa[32 * NF] : 0.0;
-                        const double gb = (l <= kb) ? rowb[32 * NF] : 0.0;
-                        const double wa = (l <= ka) ? wra[32 * NF] : 0.0;
-                        const double wb = (l <= kb) ? wrb[32 * NF] : 0.0;
-                        const double gat = (l < ka) ? ga : 0.0; // the diagonal element belongs to the row sum only
-                        const double gbt = (l < kb) ? gb : 0.0;
-                        pia[NF & 1] = fma(ga, xi[NF], pia[NF & 1]);
-                        pja[NF & 1] = fma(ga, xj[NF], pja[NF & 1]);
-                        pib[NF & 1] = fma(gb, xi[NF], pib[NF & 1]);
-                        pjb[NF & 1] = fma(gb, xj[NF], pjb[NF & 1]);
-                        jwa[NF & 1] = fma(ga, wa, jwa[NF & 1]);
-                        jwb[NF & 1] = fma(gb, wb, jwb[NF & 1]);
-                        bi[NF] = fma(gat, xka.x, bi[NF]);
-                        bj[NF] = fma(gat, xka.y, bj[NF]);
-                        bi[NF] = fma(gbt, xkb.x, bi[NF]);
-                        bj[NF] = fma(gbt, xkb.y, bj[NF]);
-                    }
-                    flush(); // previous pair
-                    jw += fma(jwb[0] + jwb[1], bscale, jwa[0] + jwa[1]);
-                    dpia = pia[0] + pia[1];
-                    dpja = pja[0] + pja[1];
-                    dpib = pib[0] + pib[1];
-                    dpjb = pjb[0] + pjb[1];
-                    dka = ka;
-                    dhasb = hasb;
-                    // Release the stage: lane 0 stores a value that depends on every shared-memory read of the stage
-                    // (a few bits of the row sums <- all G loads and of the J sums <- all weight loads), so the store cannot issue before the
-                    // last read has returned, and arrives behind it.  (An arrive placed directly behind the loads is
-                    // issued before they complete, see k3_gram.cu; deferring it to the next stage keeps two stages
-                    // per SM out of flight.)
-                    const int proof = (__double2loint(pia[0]) ^ __double2loint(pia[1]) ^ __double2loint(pib[0])) ^
-                                      (__double2loint(pib[1]) ^ __double2loint(jwa[0]) ^ __double2loint(jwa[1])) ^
-                                      (__double2loint(jwb[0]) ^ __double2loint(jwb[1]));
-                    if (lane == 0) {
-                        prf[warp] = proof;
-                        mbar_arrive(&empty[b]);
-                    }
-                } else if (lane == 0) {
-                    mbar_arrive(&empty[b]); // no rows of this warp in the stage
                 }
+                const int b = nctr % JS_NB;
+                mbar_wait(&full[b], (nctr / JS_NB) & 1);
+                ++nctr;
+                int proof = 0;
+                static_for<0, (R1 - R0) / 16>([&](auto m_c) {
+                    constexpr int M = decltype(m_c)::value;
+                    constexpr int NF = (R0 + 16 * M) / 32;
+                    if constexpr (NF < QL) {
+                        const int ka = R0 + 16 * M + 2 * warp;
+                        if (FULL || ka < kend) {
+                            const bool hasb = FULL ? true : ka + 1 < kend;
+                            const int kb = hasb ? ka + 1 : ka;
+                            const double *rowa = gbase + sh + tri32(ka) + lane;
+                            const double *rowb = hasb ? rowa + ka + 1 : rowa; // a missing row b re-reads row a against zeros
+                            [[maybe_unused]] const double *wra = gbase + cnt + tri32(ka) + lane;
+                            [[maybe_unused]] const double *wrb = hasb ? wra + ka + 1 : wra;
+                            const double2 xka = xc[ka];
+                            const double2 xkb = hasb ? xc[kb] : make_double2(0.0, 0.0);
+                            const double bscale = hasb ? 1.0 : 0.0;
+                            double pia[2] = {0.0, 0.0}, pja[2] = {0.0, 0.0}, pib[2] = {0.0, 0.0}, pjb[2] = {0.0, 0.0};
+                            double jwa[2] = {0.0, 0.0}, jwb[2] = {0.0, 0.0};
+#pragma unroll
+                            for (int q = 0; q < NF; ++q) {
+                                const double ga = rowa[32 * q], gb = rowb[32 * q];
+                                double wa, wb;
+                                if constexpr (WSM) {
+                                    wa = wra[32 * q];
+                                    wb = wrb[32 * q];
+                                } else {
+                                    wa = wga[q];
+                                    wb = wgb[q];
+                                }
+                                pia[q & 1] = fma(ga, xi[q], pia[q & 1]);
+                                pja[q & 1] = fma(ga, xj[q], pja[q & 1]);
+                                pib[q & 1] = fma(gb, xi[q], pib[q & 1]);
+                                pjb[q & 1] = fma(gb, xj[q], pjb[q & 1]);
+                                jwa[q & 1] = fma(ga, wa, jwa[q & 1]);
+                                jwb[q & 1] = fma(gb, wb, jwb[q & 1]);
+                                bi[q] = fma(ga, xka.x, bi[q]);
+                                bj[q] = fma(ga, xka.y, bj[q]);
+                                bi[q] = fma(gb, xkb.x, bi[q]);
+                                bj[q] = fma(gb, xkb.y, bj[q]);
+                            }
+                            {
+                                const int l = lane + 32 * NF;
+                                const double ga = (l <= ka) ? rowa[32 * NF] : 0.0;
+                                const double gb = (l <= kb) ? rowb[32 * NF] : 0.0;
+                                double wa, wb;
+                                if constexpr (WSM) {
+                                    wa = (l <= ka) ? wra[32 * NF] : 0.0;
+                                    wb = (l <= kb) ? wrb[32 * NF] : 0.0;
+                                } else {
+                                    wa = wga[NF];
+                                    wb = wgb[NF];
+                                }
+                                const double gat = (l < ka) ? ga : 0.0; // the diagonal element belongs to the row sum only
+                                const double gbt = (l < kb) ? gb : 0.0;
+                                pia[NF & 1] = fma(ga, xi[NF], pia[NF & 1]);
+                                pja[NF & 1] = fma(ga, xj[NF], pja[NF & 1]);
+                                pib[NF & 1] = fma(gb, xi[NF], pib[NF & 1]);
+                                pjb[NF & 1] = fma(gb, xj[NF], pjb[NF & 1]);
+                                jwa[NF & 1] = fma(ga, wa, jwa[NF & 1]);
+                                jwb[NF & 1] = fma(gb, wb, jwb[NF & 1]);
+                                bi[NF] = fma(gat, xka.x, bi[NF]);
+                                bj[NF] = fma(gat, xka.y, bj[NF]);
+                                bi[NF] = fma(gbt, xkb.x, bi[NF]);
+                                bj[NF] = fma(gbt, xkb.y, bj[NF]);
+                            }
+                            flush(); // previous pair
+                            jw += fma(jwb[0] + jwb[1], bscale, jwa[0] + jwa[1]);
+                            dpia = pia[0] + pia[1];
+                            dpja = pja[0] + pja[1];
+                            dpib = pib[0] + pib[1];
+                            dpjb = pjb[0] + pjb[1];
+                            dka = ka;
+                            dhasb = hasb;
+                            proof ^= (__double2loint(pia[0]) ^ __double2loint(pia[1]) ^ __double2loint(pib[0])) ^
+                                     (__double2loint(pib[1]) ^ __double2loint(jwa[0]) ^ __double2loint(jwa[1])) ^
+                                     (__double2loint(jwb[0]) ^ __double2loint(jwb[1]));
+                        }
+                    }
+                });
+                // Release the stage: lane 0 stores a value that depends on every shared-memory read of the stage (a
+                // few bits of the row sums <- all G loads and of the J sums <- all weight loads), so the store cannot
+                // issue before the last read has returned, and arrives behind it.  (An arrive placed directly behind
+                // the loads is issued before they complete, see k3_gram.cu; deferring it to the next stage keeps two
+                // stages per SM out of flight.)
+                if (lane == 0) {
+                    prf[warp] = proof;
+                    mbar_arrive(&empty[b]);
                 }
             }
         });
@@ -401,7 +443,7 @@ cudaError_t launch_stream_q(const JkParams &p, int smem, int num_sms, cudaStream
 
 int jk_stream_max_nmo() { return 256; }
 
-// Stages of one column: blocks of JS_ROWS whole packed rows and their J weights, placed back to back in a ring of
+// Stages of one column: blocks of whole packed rows (js_row0) and their J weights, placed back to back in a ring of
 // `stage_doubles` doubles (all the shared memory left: the bytes in flight per SM bound the HBM throughput).
 // Returns the number of stages (0: does not fit); fills srow[0..nst], ring (= stages that fit at least) and the sizes.
 int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_bytes)
@@ -411,13 +453,14 @@ int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_
     const int cap = ((227 * 1024 - fixed) / 8) & ~1;
     int nst = 0, biggest = 0;
     srow[0] = 0;
-    for (int k = 0; k < nmo; k += JS_ROWS) { // the consumers' stage structure is compiled in: JS_ROWS rows per stage
-        const int k1 = k + JS_ROWS < nmo ? k + JS_ROWS : nmo;
+    for (int st = 0; js_row0(st) < nmo; ++st) { // the consumers' stage structure is compiled in (js_row0)
+        const int k = js_row0(st), k1 = js_row0(st + 1) < nmo ? js_row0(st + 1) : nmo;
         const int n = k1 * (k1 + 1) / 2 - k * (k + 1) / 2;
-        biggest = n > biggest ? n : biggest;
+        const int need = st < JS_WSM ? 2 * ((n + 3) & ~1) : (n + 3) & ~1; // G rows (+ shift / pad) | weight rows
+        biggest = need > biggest ? need : biggest;
         srow[++nst] = k1;
     }
-    const int slot = 2 * ((biggest + 2 + 1) & ~1); // G rows (+ alignment shift / pad element) | weight rows
+    const int slot = biggest;
     if (cap / slot < 3 || nst > JS_MAX_STAGES) return 0;
     *ring = cap / slot;
     *stage_doubles = cap;
