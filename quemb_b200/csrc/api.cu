@@ -1788,16 +1788,15 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     }
     const int nch = (int)crow.size() - 1;
     // single-pass streaming kernel (jk_stream.cu) when the fragment fits it; QEMB_JK_KERNEL=rows forces jk.cu
-    int srow[64] = {0}, nst = 0, ring = 0, stage_doubles = 0, stream_smem = 0;
+    int nst = 0, ring_doubles = 0, stream_smem = 0;
     {
         const char *force = std::getenv("QEMB_JK_KERNEL");
         const bool want_rows = force && std::strcmp(force, "rows") == 0;
         if (!want_rows && nmo <= jk_stream_max_nmo() && (reinterpret_cast<uintptr_t>(w->G_last) & 15) == 0)
-            nst = jk_stream_plan((int)nmo, srow, &ring, &stage_doubles, &stream_smem);
+            nst = jk_stream_plan((int)nmo, &ring_doubles, &stream_smem);
     }
     const bool stream = nst > 0;
-    if (stream) crow.assign(srow, srow + nst + 1);
-    // inputs: D (nmo^2) | dpk (npair) | crow (jk.cu chunk table or jk_stream.cu stage table)
+    // inputs: D (nmo^2) | dpk (npair) | crow (jk.cu chunk table)
     // (dpk 16-byte aligned and padded by two doubles: jk_stream.cu copies whole rows of it with 16-byte bulk copies)
     const size_t oD = 0, oP = ((size_t)nmo * nmo * 8 + 15) / 16 * 16, oC = oP + ((size_t)npair + 2) * 8;
     const size_t in_bytes = oC + crow.size() * 4;
@@ -1823,10 +1822,8 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     p.dpk = reinterpret_cast<const double *>(static_cast<char *>(w->jk_in.p) + oP);
     p.crow = reinterpret_cast<const int *>(static_cast<char *>(w->jk_in.p) + oC);
     p.nchunks = nch;
-    p.srow = p.crow;
     p.nstages = nst;
-    p.ring = ring;
-    p.stage_doubles = stage_doubles;
+    p.ring_doubles = ring_doubles;
     p.njp = njp1;
     p.Jp = w->jk_scratch.as<double>();
     p.R1 = p.Jp + njp;

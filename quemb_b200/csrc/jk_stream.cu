@@ -1,4 +1,4 @@
-// jk_stream.cu -- J/K from the device-resident (ij|kl), single-pass streaming kernel (nmo <= 256).
+// jk_stream.cu -- J/K from the device-resident (ij|kl), single-pass streaming kernel (nmo <= 255).
 //
 // Same contraction and outputs as jk.cu (reference consumers: get_veff, src/quemb/molbe/helper.py:28-69, and the
 // two-electron part of update_ebe_hf, src/quemb/molbe/pfrag.py:327-390):
@@ -7,10 +7,10 @@
 // triangle is used for five FMAs from ONE shared-memory read:
 //   pa[k]  += g x[l]   (x = D[:,i] and D[:,j]: row sums, reduced over the lanes once per row pair)
 //   vb[l]  += g x[k]   (column sums, kept in the lane's registers for the whole column, l = lane + 32 q)
-//   J      += g w[k,l] (packed weights D[k,l] (2 - delta_kl), coalesced loads issued one row pair ahead)
+//   J      += g w[k,l] (packed weights D[k,l] (2 - delta_kl), staged in shared memory next to the rows)
 // jk.cu reads every element three times from shared memory, in three differently shaped loops, behind two CTA
 // barriers per chunk (27 % of the HBM peak, 38 instructions per 32 elements); here a warp owns whole rows (lanes
-// along l, conflict free), one row pair costs ~12 instructions per 64 elements plus one 4-value butterfly, and
+// along l, conflict free), one row pair costs ~14 instructions per 64 elements plus one 4-value butterfly, and
 // there is no CTA barrier inside a column:
 //   * producer warp: one 1-D bulk copy (cp.async.bulk, SASS UBLKCP) per stage = a block of whole packed rows,
 //     and one of the same rows of the J weights, completion counted on the stage's "full" mbarrier; stages are
@@ -107,7 +107,7 @@ __device__ __forceinline__ void pair_of(int64_t r, int &i, int &j)
 }
 } // namespace
 
-// shared memory: ring of stage_doubles doubles, a stage = [G rows | weight rows] placed back to back (wrapping to 0
+// shared memory: ring of ring_doubles doubles, a stage = [G rows | weight rows] placed back to back (wrapping to 0
 //                when the next one does not fit) | slab[JS_NW][nmoP] double2 | x2[2][nmoP] double2 | va2[nmoP] double2 |
 //                jws[JS_NW] | full[JS_NB], empty[JS_NB]
 // Stage S = packed rows [js_row0(S), min(js_row0(S + 1), nmo)); in every 16 rows of it warp w owns the row pair
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
     constexpr int NMOP = 32 * QL;
     constexpr int NSTAGE = js_stages(32 * QL); // stages that start at or below row 32 (QL - 1) always exist
     extern __shared__ __align__(16) double js_smem[];
-    const int cap = p.stage_doubles; // ring capacity in doubles (even); stages are placed back to back
+    const int cap = p.ring_doubles; // ring capacity in doubles (even); stages are placed back to back
     double *ringbuf = js_smem;
     double2 *slab = reinterpret_cast<double2 *>(ringbuf + cap);
     double2 *x2 = slab + JS_NW * NMOP;
@@ -443,27 +443,25 @@ cudaError_t launch_stream_q(const JkParams &p, int smem, int num_sms, cudaStream
 
 int jk_stream_max_nmo() { return 256; }
 
-// Stages of one column: blocks of whole packed rows (js_row0) and their J weights, placed back to back in a ring of
-// `stage_doubles` doubles (all the shared memory left: the bytes in flight per SM bound the HBM throughput).
-// Returns the number of stages (0: does not fit); fills srow[0..nst], ring (= stages that fit at least) and the sizes.
-int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_bytes)
+// Stages of one column: blocks of whole packed rows (js_row0) and their J weights, placed back to back in a ring that
+// takes all the shared memory left (the bytes in flight per SM bound the HBM throughput).  Returns the number of stages
+// (0: does not fit); fills the ring capacity in doubles and the dynamic shared-memory size.  Three of the largest stage
+// must fit: with two, a stage that wraps to the start of the ring can overlap the one still being read (deadlock).
+int jk_stream_plan(int nmo, int *ring_doubles, int *smem_bytes)
 {
     const int QL = (nmo + 31) / 32, nmoP = 32 * QL;
     const int fixed = (JS_NW + 3) * nmoP * 16 + 2 * JS_NW * 8 + 2 * JS_MAX_STAGES * 4 + 2 * JS_NB * 8 + 64;
     const int cap = ((227 * 1024 - fixed) / 8) & ~1;
     int nst = 0, biggest = 0;
-    srow[0] = 0;
     for (int st = 0; js_row0(st) < nmo; ++st) { // the consumers' stage structure is compiled in (js_row0)
         const int k = js_row0(st), k1 = js_row0(st + 1) < nmo ? js_row0(st + 1) : nmo;
         const int n = k1 * (k1 + 1) / 2 - k * (k + 1) / 2;
         const int need = st < JS_WSM ? 2 * ((n + 3) & ~1) : (n + 3) & ~1; // G rows (+ shift / pad) | weight rows
         biggest = need > biggest ? need : biggest;
-        srow[++nst] = k1;
+        ++nst;
     }
-    const int slot = biggest;
-    if (cap / slot < 3 || nst > JS_MAX_STAGES) return 0;
-    *ring = cap / slot;
-    *stage_doubles = cap;
+    if (cap / biggest < 3 || nst > JS_MAX_STAGES) return 0;
+    *ring_doubles = cap;
     *smem_bytes = cap * 8 + fixed;
     return nst;
 }

@@ -87,9 +87,8 @@ struct JkParams {
     double *Jp;        // npair x njp partial sums of J
     int njp;           // jk_warps() (jk.cu) or 1 (jk_stream.cu)
     double *R1, *R2;   // npair x nmo (row r at r*nmo)
-    // jk_stream.cu: stage table (stage st = packed rows [srow[st], srow[st+1])), ring depth and slot size
-    const int *srow;
-    int nstages, ring, stage_doubles;
+    // jk_stream.cu: stages per column and capacity of the shared-memory ring in doubles (jk_stream_plan)
+    int nstages, ring_doubles;
 };
 cudaError_t launch_jk(const JkParams &p, double *J, double *K, int64_t ldo, int num_sms, cudaStream_t s);
 int jk_max_nmo();
@@ -97,7 +96,7 @@ int jk_chunk_doubles();
 int jk_warps();
 // single-pass streaming kernel (jk_stream.cu), nmo <= jk_stream_max_nmo(), G 16-byte aligned
 int jk_stream_max_nmo();
-int jk_stream_plan(int nmo, int *srow, int *ring, int *stage_doubles, int *smem_bytes);
+int jk_stream_plan(int nmo, int *ring_doubles, int *smem_bytes); // stages per column, 0 = does not fit
 cudaError_t launch_jk_stream(const JkParams &p, int smem, int num_sms, cudaStream_t s);
 cudaError_t launch_jk_reduce(const JkParams &p, double *J, double *K, int64_t ldo, cudaStream_t s);
 
