@@ -35,6 +35,9 @@ __device__ __forceinline__ void static_for(F &&f)
         static_for<I + 1, N>(f);
     }
 }
+#ifndef JS_COMPUTE
+#define JS_COMPUTE 1 // 0: consumers only wait for and release the stages (data-path ceiling of the ring, wrong results)
+#endif
 constexpr int JS_NW = 8;                      // consumer warps: one row pair each per 16 packed rows of a stage
 constexpr int JS_THREADS = 32 * (JS_NW + 1);  // + producer warp
 constexpr int JS_NB = 16;                     // mbarrier pairs = stages in flight at most
@@ -304,7 +307,7 @@ __global__ void __launch_bounds__(JS_THREADS, 1) jk_stream_kernel(JkParams p)
                     constexpr int NF = (R0 + 16 * M) / 32;
                     if constexpr (NF < QL) {
                         const int ka = R0 + 16 * M + 2 * warp;
-                        if (FULL || ka < kend) {
+                        if (JS_COMPUTE && (FULL || ka < kend)) {
                             const bool hasb = FULL ? true : ka + 1 < kend;
                             const int kb = hasb ? ka + 1 : ka;
                             const double *rowa = gbase + sh + tri32(ka) + lane;
