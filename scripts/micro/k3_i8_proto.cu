@@ -27,7 +27,10 @@ constexpr int S = 7;          // slices
 constexpr int TM = 128;       // A tile: pairs i (TMEM lanes)
 constexpr int TN = 64;        // B tile: pairs j (TMEM columns per accumulator)
 constexpr int KC = 128;       // bytes (= int8 elements) of K per stage = one swizzle row
-constexpr int A_RING = 4;
+#ifndef A_RING_DEF
+#define A_RING_DEF 4
+#endif
+constexpr int A_RING = A_RING_DEF;
 constexpr int A_BYTES = TM * KC, B_BYTES = TN * KC;
 constexpr int SMEM_BYTES = A_RING * A_BYTES + 2 * S * B_BYTES + 1024;
 constexpr int NTHREADS = 32 * 6;
@@ -58,6 +61,13 @@ __device__ __forceinline__ void tma_load(void *dst, const CUtensorMap *map, int 
 {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(s32(dst)),
                  "l"(map), "r"(c0), "r"(c1), "r"(s32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void umma(uint32_t dcol, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(dcol),
+                 "l"(da), "l"(db), "r"(idesc), "r"(acc)
                  : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar)
@@ -186,19 +196,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
                     for (int a = 0; a < S; ++a) {
                         mbar_wait(&fullA[sa], pa);
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        const uint32_t abase = s32(sA + sa * A_BYTES);
+                        const uint64_t da0 = make_desc(s32(sA + sa * A_BYTES));
+                        const uint64_t db0 = make_desc(s32(sB + sb * S * B_BYTES));
+                        const bool first = kc == 0 && a == 0;
                         for (int b = 0; b + a < S; ++b) {
-                            const uint32_t bbase = s32(sB + (sb * S + b) * B_BYTES);
+                            const uint64_t db = db0 + (uint64_t)(b * (B_BYTES >> 4)); // next slice: start address + 8 KB
                             const uint32_t dcol = tacc + (uint32_t)((a + b) * TN);
-#pragma unroll
-                            for (int k4 = 0; k4 < KC / 32; ++k4) {
-                                const uint64_t da = make_desc(abase + 32 * k4), db = make_desc(bbase + 32 * k4);
-                                const uint32_t acc = !(kc == 0 && a == 0 && k4 == 0);
-                                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                             "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(dcol),
-                                             "l"(da), "l"(db), "r"(idesc), "r"(acc)
-                                             : "memory");
-                            }
+                            umma(dcol, da0, db, idesc, first ? 0u : 1u);
+                            umma(dcol, da0 + 2, db + 2, idesc, 1u); // + 32 bytes of K inside the swizzle row
+                            umma(dcol, da0 + 4, db + 4, idesc, 1u);
+                            umma(dcol, da0 + 6, db + 6, idesc, 1u);
                         }
                         umma_commit(&emptyA[sa]); // slot free once the MMAs above have read it
                         if (++sa == A_RING) {
@@ -228,19 +235,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
             const int ei = i < p.npair ? p.expo[i] : 0;
             for (int c0 = 0; c0 < TN; c0 += 8) {
                 double g[8];
+                uint32_t v[S][8];
+#pragma unroll
+                for (int d = 0; d < S; ++d) { // all S accumulators of these 8 columns in flight, one wait
+                    const uint32_t addr = tacc + ((uint32_t)lbase << 16) + (uint32_t)(d * TN + c0);
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(v[d][0]), "=r"(v[d][1]), "=r"(v[d][2]), "=r"(v[d][3]), "=r"(v[d][4]), "=r"(v[d][5]), "=r"(v[d][6]),
+                                   "=r"(v[d][7])
+                                 : "r"(addr));
+                }
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
                 for (int q = 0; q < 8; ++q) g[q] = 0.0;
 #pragma unroll
                 for (int d = S - 1; d >= 0; --d) { // small terms first
-                    uint32_t v[8];
-                    const uint32_t addr = tacc + ((uint32_t)lbase << 16) + (uint32_t)(d * TN + c0);
-                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
-                                 : "r"(addr));
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     const double w = ldexp(1.0, -(7 * d + 12));
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) g[q] = fma((double)(int32_t)v[q], w, g[q]);
+                    for (int q = 0; q < 8; ++q) g[q] = fma((double)(int32_t)v[d][q], w, g[q]);
                 }
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
@@ -248,7 +259,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
                     if (i < p.npair && j < p.npair && j <= i) {
                         const double val = ldexp(g[q], ei + p.expo[j]);
                         p.G[i + p.ldg * j] = val;
+#ifndef NO_MIRROR
                         p.G[j + p.ldg * i] = val;
+#endif
                     }
                 }
             }
