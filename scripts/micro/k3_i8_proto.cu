@@ -23,7 +23,10 @@
 #include <cuda_runtime.h>
 #include <vector>
 
-constexpr int S = 7;          // slices
+#ifndef S_DEF
+#define S_DEF 7
+#endif
+constexpr int S = S_DEF;      // slices (S * TN <= 512 TMEM columns)
 constexpr int TM = 128;       // A tile: pairs i (TMEM lanes)
 constexpr int TN = 64;        // B tile: pairs j (TMEM columns per accumulator)
 constexpr int KC = 128;       // bytes (= int8 elements) of K per stage = one swizzle row
