@@ -275,6 +275,7 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
 
     b = FragmentERIBuilder(local_rank)
     ctx = b.ctx
+    ctx.set_k3_int8_slices(args.k3_int8)
     # raw (un-whitened) device copy kept aside so that every step redoes the metric application
     t0 = time.perf_counter()
     raw = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, ctx=ctx)
@@ -429,7 +430,9 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
                    "partition": (f"fragments LPT over {world} rank(s), no collective on the fragment path; the one-off metric "
                                  "application is split over the ranks by columns and exchanged with NCCL broadcasts"
                                  if world > 1 else "1 rank"),
-                   "fragments_rank0": len(mine)},
+                   "fragments_rank0": len(mine),
+                   "k3": (f"opt-in int8-slice K3, {args.k3_int8} slices (roofline.achieved counts the FP64-equivalent flops)"
+                          if args.k3_int8 else "FP64 DMMA (default)")},
         "fragments_per_s": nfrag / t_dev,
         "roofline": {"bound": "tensor", "kernel": "gram_kernel (K3: G = X^T X, FP64 DMMA.8x8x4)",
                      "achieved": achieved, "peak": peak_sust, "unit": "TFLOP/s",
@@ -463,6 +466,8 @@ def main() -> None:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c32h66", choices=["c32h66", "octane", "tiny"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--k3-int8", type=int, default=0, choices=[0, 7, 8],
+                    help="opt-in K3 on the int8 tensor cores with that many slices (default 0: FP64 tensor path)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

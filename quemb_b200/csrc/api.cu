@@ -78,6 +78,8 @@ struct qemb_ctx {
     // mode 1 only: the last `full_frac` of the columns cross PCIe whole (rows 0..n) and are not mirrored on the host:
     // balances the copy engine (slack) against the host threads (the bottleneck of a pure triangle transfer)
     double full_frac = 0.0;
+    // 0: K3 on the FP64 tensor path (default, the parity reference); 7 / 8: opt-in int8-slice K3 (k3_int8.cu)
+    int k3_slices = 0;
     int num_sms = 148;
     int64_t h2d_bytes = 0, d2h_bytes = 0; // bytes handed to the copy engines (uploads / G transfers)
     // host-bound G transfers whose host mirror has not finished yet (qemb_ctx_synchronize waits for them)
@@ -321,6 +323,7 @@ struct qemb_workspace {
     DevBuf gram_partial; // split-K partial tiles of K3 for small fragments
     // J/K consumer (jk.cu)
     DevBuf jk_in, jk_scratch, jk_out;
+    DevBuf gram_i8; // scratch of the opt-in int8-slice K3
     cudaEvent_t jk_ev[2] = {nullptr, nullptr};
     float jk_ms = 0.f;
     // gram tile lists by number of row tiles
@@ -370,6 +373,10 @@ extern "C" int qemb_ctx_create(int device, qemb_ctx **out)
     c->device = device;
     c->num_sms = prop.multiProcessorCount;
     if (const char *e = std::getenv("QEMB_FULL_COLUMN_FRACTION")) c->full_frac = std::min(1.0, std::max(0.0, std::atof(e)));
+    if (const char *e = std::getenv("QEMB_K3_INT8")) {
+        const int n = std::atoi(e);
+        c->k3_slices = (n == 7 || n == 8) ? n : 0;
+    }
     CU(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->prep, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
@@ -436,6 +443,13 @@ extern "C" int qemb_ctx_set_full_column_fraction(qemb_ctx *c, double frac)
 {
     REQ(c && frac >= 0.0 && frac <= 1.0, "fraction must be in [0, 1]");
     c->full_frac = frac;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_set_k3_int8_slices(qemb_ctx *c, int slices)
+{
+    REQ(c && (slices == 0 || slices == 7 || slices == 8), "slices must be 0 (FP64 K3), 7 or 8");
+    c->k3_slices = slices;
     return QEMB_OK;
 }
 
@@ -1028,6 +1042,7 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     cudaEventDestroy(w->ev2s);
     for (auto &e : w->jk_ev)
         if (e) cudaEventDestroy(e);
+    w->gram_i8.release();
     w->jk_in.release();
     w->gram_partial.release();
     w->jk_scratch.release();
@@ -1517,8 +1532,23 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         CU(cudaEventRecord(w->ev[3], cs));
         w->ev_valid[3] = true;
     }
-    CU(launch_gram(p, w->ctx->num_sms, cs));
-    w->ctx->launches += nsplit > 1 ? 2 : 1;
+    if (w->ctx->k3_slices && !accumulate) { // opt-in int8-slice K3 (k3_int8.cu); the accumulating form stays FP64
+        GramI8Params q;
+        q.X = p.X;
+        q.ldx = p.ldx;
+        q.nrows = (int)w->mrows;
+        q.npair = s.npair;
+        q.G = dst;
+        q.ldg = ld;
+        q.slices = w->ctx->k3_slices;
+        TRY(w->gram_i8.reserve(gram_i8_scratch_bytes(q.nrows, q.npair, q.slices)));
+        q.scratch = w->gram_i8.as<int8_t>();
+        CU(launch_gram_int8(q, w->ctx->num_sms, cs));
+        w->ctx->launches += 3;
+    } else {
+        CU(launch_gram(p, w->ctx->num_sms, cs));
+        w->ctx->launches += nsplit > 1 ? 2 : 1;
+    }
     if (w->ctx->timing) {
         CU(cudaEventRecord(w->ev[4], cs));
         w->ev_valid[4] = true;

@@ -28,6 +28,21 @@ cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s);
 int64_t build_gram_tiles(int nt, int2 *out /* nt*(nt+1)/2 */);
 constexpr int GRAM_TILE = 128;
 
+// ---- K3, opt-in int8-slice variant (k3_int8.cu): same G, tcgen05 int8 tensor cores -------------------------
+struct GramI8Params {
+    const double *X;   // (ldx x npair) column-major, rows = auxiliary index, `nrows` valid (zero padded) rows
+    int64_t ldx;
+    int nrows;
+    int64_t npair;
+    double *G;         // npair x npair, ld = ldg (both triangles written)
+    int64_t ldg;
+    int slices;        // 7 (1e-12 of max|G|) or 8 (1e-14)
+    int8_t *scratch;   // gram_i8_scratch_bytes(...) bytes, 256-byte aligned
+};
+int gram_i8_naux_pad(int nrows);
+size_t gram_i8_scratch_bytes(int nrows, int64_t npair, int slices);
+cudaError_t launch_gram_int8(const GramI8Params &p, int num_sms, cudaStream_t s);
+
 // ---- K1 / K2a: grouped gather GEMM --------------------------------------------------------------
 //   C[:, ccol[n]] = sum_k  Asrc[:, acol[k]] * TA[brow[k], bcol[n]]        (k < K, n < N of the group)
 struct GatherGroup {

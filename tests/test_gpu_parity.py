@@ -409,6 +409,43 @@ def test_jk_stream_kernel_all_block_structures(q, monkeypatch):
             assert np.array_equal(vj, vj_r)  # both calls ran the chunked kernel
 
 
+@pytest.mark.parametrize("slices,rel", [(8, 2e-13), (7, 2e-11)])
+def test_k3_int8_slices_opt_in(q, slices, rel):
+    """Opt-in K3 on the int8 tensor cores (k3_int8.cu): error-free split of X into 7-bit slices, exact int32 products,
+    FP64 recombination.  Against the reference's golden (ij|kl) and against the FP64 K3 of this library, on the
+    goldens and on a fragment large enough for many tiles and k chunks; the default (0 slices) is restored."""
+    ctx = q.default_context(0)
+    cases = []
+    for name in ("chain_small", "lattice_small"):
+        g = Golden(name)
+        T = _tensor(q, g)
+        L = q.GPU_MatrixHandle(g.L)
+        for f in range(g.n_frag):
+            fr = g.frag(f)
+            cases.append((T, fr["TA"], g.S_abs, L, g.eps, fr["G"]))
+    p = syn.make_chain_problem(n_units=10, ao_per_unit=16, n_end=3, naux=333, frag_halfwidth=2, n_bath=40,
+                               sigma=0.94, seed=77, n_frag=6)
+    Tp = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable)
+    Lp = q.GPU_MatrixHandle(p.L_PQ)
+    cases.append((Tp, p.TAs[3], p.S_abs, Lp, p.MO_coeff_epsilon, None))
+    try:
+        for T, TA, S_abs, L, eps, G_gold in cases:
+            ctx.set_k3_int8_slices(0)
+            G64 = q.transform_integral(T, TA, S_abs, L, eps)
+            ctx.set_k3_int8_slices(slices)
+            G8 = q.transform_integral(T, TA, S_abs, L, eps)
+            scale = max(1.0, np.abs(G64).max())
+            assert G8.shape == G64.shape
+            assert np.abs(G8 - G64).max() <= rel * scale
+            assert np.array_equal(G8, G8.T)
+            if G_gold is not None:
+                assert np.abs(G8 - G_gold).max() <= max(TOL, rel * scale)
+            G8b = q.transform_integral(T, TA, S_abs, L, eps)
+            assert np.array_equal(G8, G8b)  # integer products: bitwise repeatable
+    finally:
+        ctx.set_k3_int8_slices(0)
+
+
 def test_dense_int_direct_DF_on_the_same_kernels(q):
     """the unscreened limit against a numpy restatement of integral_direct_DF
     (eri_onthefly.py:127-145)."""
