@@ -1532,7 +1532,9 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         CU(cudaEventRecord(w->ev[3], cs));
         w->ev_valid[3] = true;
     }
-    if (w->ctx->k3_slices && !accumulate) { // opt-in int8-slice K3 (k3_int8.cu); the accumulating form stays FP64
+    // opt-in int8-slice K3 (k3_int8.cu); the accumulating form stays FP64, and so do slabs deep enough to overflow the
+    // exact int32 sums (slices * rows * 127^2 < 2^31)
+    if (w->ctx->k3_slices && !accumulate && (int64_t)w->ctx->k3_slices * w->mrows * 16129 < (int64_t)2147483647) {
         GramI8Params q;
         q.X = p.X;
         q.ldx = p.ldx;
