@@ -446,6 +446,35 @@ def test_k3_int8_slices_opt_in(q, slices, rel):
         ctx.set_k3_int8_slices(0)
 
 
+@pytest.mark.parametrize("slices", [7, 8])
+def test_k3_int8_bit_exact_against_its_restatement(q, slices):
+    """The int8-slice K3 is integer work plus a fixed-order FP64 recombination: given the X the device holds
+    (qemb_fragment_get_sym after the transform), the numpy restatement oracle/k3_int8_oracle.py must reproduce the
+    device result bit for bit."""
+    import ctypes
+
+    from oracle import k3_int8_oracle as ko
+    from quemb_b200._lib import c_i64, lib, ptr
+
+    ctx = q.default_context(0)
+    ws = q.default_workspace(ctx)
+    try:
+        ctx.set_k3_int8_slices(slices)
+        for name in ("chain_small", "lattice_small"):
+            g = Golden(name)
+            T = _tensor(q, g)
+            L = q.GPU_MatrixHandle(g.L)
+            for f in range(g.n_frag):
+                fr = g.frag(f)
+                G8 = q.transform_integral(T, fr["TA"], g.S_abs, L, g.eps, ws=ws)
+                naux, npair = g.L.shape[0], G8.shape[0]
+                X = np.empty((naux, npair), order="F")
+                assert lib().qemb_fragment_get_sym(ws._h, ptr(X), c_i64(naux)) == 0
+                assert np.array_equal(G8, ko.gram_int8(X, slices)), (name, f)
+    finally:
+        ctx.set_k3_int8_slices(0)
+
+
 def test_dense_int_direct_DF_on_the_same_kernels(q):
     """the unscreened limit against a numpy restatement of integral_direct_DF
     (eri_onthefly.py:127-145)."""

@@ -132,3 +132,30 @@ def test_consumer_oracle_identity():
     n_frag = max(1, nmo // 2)
     e2 = co.ebe_hf_e2(G, D, n_frag)
     assert np.abs(e2 - np.einsum("ij,ij->i", D[:n_frag], 2 * vj[:n_frag] - vk[:n_frag])).max() <= 1e-12
+
+
+def test_k3_int8_oracle_split_is_error_free_and_within_its_bound():
+    """The restatement of the opt-in int8-slice K3: the split reconstructs X exactly (slices + remainder), the
+    integer sums stay inside int32, and the recombined matrix is within the worst-case truncation bound of the FP64
+    product (and far inside it in practice)."""
+    from oracle import k3_int8_oracle as ko
+
+    rng = np.random.default_rng(5)
+    naux, npair = 300, 90
+    X = rng.standard_normal((naux, npair)) * np.exp(-6 * rng.random(npair))[None, :] * np.exp(-4 * rng.random(naux))[:, None]
+    X[:, 7] = 0.0                                   # an all-zero pair
+    X[3, 11] = 0.75 * 2.0 ** 10                     # exactly representable extremes
+    G = X.T @ X
+    for S in (7, 8):
+        e, D, R = ko.slice_int8(X, S)
+        rec = sum(D[a] * 2.0 ** -(7 * a + 6) for a in range(S)) + R * 2.0 ** -(7 * S - 1)
+        assert np.array_equal(np.ldexp(rec, e[None, :]), X)
+        assert all(np.abs(d).max() <= 127 and np.array_equal(d, np.trunc(d)) for d in D) and np.abs(D[0]).max() <= 63
+        assert np.abs(R).max() < 1.0
+        G8 = ko.gram_int8(X, S)
+        assert np.array_equal(G8, G8.T)
+        scale = np.ldexp(1.0, e[:, None] + e[None, :])
+        err = np.abs(G8 - G) / scale
+        assert err.max() <= ko.truncation_bound(naux, S) + 4 * naux * 2.0 ** -53
+        assert np.abs(G8 - G).max() <= (1e-11 if S == 7 else 1e-13) * np.abs(G).max()
+    assert ko.truncation_bound(2716, 7) < 1.5e-10 and ko.truncation_bound(2716, 8) < 1.5e-12  # why 7 slices are not the default
