@@ -209,10 +209,11 @@ int qemb_ctx_set_output_mode(qemb_ctx *, int mode);
  * pure triangle transfer) to the copy engine, which has slack while the kernels run. */
 int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
 
-/* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 7 or 8 = error-free
- * split of X into that many 7-bit integer slices multiplied on the int8 tensor cores with exact int32 accumulation
- * and recombined in FP64 (k3_int8.cu).  Measured deviation from the FP64 product: 1.3e-12 (7) / 1.1e-14 (8) of
- * max|G|, at 1.9x / 1.3x the speed of the FP64 tensor peak.  Default: QEMB_K3_INT8 or 0.  The accumulating transform
+/* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 6, 7 or 8 =
+ * error-free split of X into that many 7-bit integer slices (digits by round to nearest) multiplied on the int8 tensor
+ * cores with exact int32 accumulation and recombined in FP64 (k3_int8.cu).  Deviation from the exact product on
+ * K3-shaped operands, as a fraction of max|G|: about 3e-12 (6), 1e-14 (7), FP64 rounding level (8)
+ * (profiles/k3_int8_parity_study_r1.jsonl).  Default: QEMB_K3_INT8 or 0.  The accumulating transform
  * (out_is_device == 2) always uses the FP64 path. */
 int qemb_ctx_set_k3_int8_slices(qemb_ctx *ctx, int slices);
 /* number of host worker threads of the library (QEMB_HOST_THREADS, default: cores in the affinity mask - 1) */

@@ -1,8 +1,9 @@
 // k3_int8.cu -- OPT-IN K3 (G = X^T X) through 7-bit integer slices on the int8 tensor cores (tcgen05.mma kind::i8,
-// SASS UTCIMMA, int32 accumulators in TMEM); off by default (qemb_ctx_set_k3_int8_slices / QEMB_K3_INT8 = 7 or 8).
+// SASS UTCIMMA, int32 accumulators in TMEM); off by default (qemb_ctx_set_k3_int8_slices / QEMB_K3_INT8 = 6, 7 or 8).
 //
 // Same result as k3_gram.cu (reference: G = X^T X in FP64, cpp:620) up to the dropped slices:
-//   X[:, j] = 2^e_j * sum_{a<S} 2^-(7a+6) D_a[:, j]  (+ remainder below 2^-(7S-1)),  D_a int8, the split is error free
+//   X[:, j] = 2^e_j * sum_{a<S} 2^-(7a+6) D_a[:, j]  (+ remainder <= 2^-7S),  D_a int8 in [-64, 64] (digits by round to
+//             nearest: the split is error free and the dropped terms carry no sign bias)
 //   G_ij    = 2^(e_i+e_j) * sum_{d<S} 2^-(7d+12) * sum_{a+b=d} <D_a[:, i], D_b[:, j]>     (inner sums exact in int32)
 // measured on K3-shaped operands: S = 7 -> 1.3e-12 of max|G|, S = 8 -> 1.1e-14 (profiles/k3_i8_proto_r1.txt), at
 // 1.9x / 1.3x the speed of the FP64 tensor peak.  The FP64 DMMA kernel stays the default and the parity reference.
@@ -98,7 +99,7 @@ __global__ void slice_kernel(const double *X, int64_t ldx, int naux, int naux_pa
         double scale = 64.0;
 #pragma unroll
         for (int a = 0; a < S; ++a) {
-            const double t = trunc(r * scale);
+            const double t = rint(r * scale); // nearest, ties to even: digits in [-64, 64], no sign bias in the dropped terms
             r = r * scale - t; // exact
             row[a * naux_pad + p] = (int8_t)t;
             scale = 128.0;
@@ -344,6 +345,7 @@ size_t gram_i8_scratch_bytes(int nrows, int64_t npair, int slices)
 cudaError_t launch_gram_int8(const GramI8Params &p, int num_sms, cudaStream_t s)
 {
     if (p.npair <= 0) return cudaSuccess;
+    if (p.slices == 6) return launch_i8<6>(p, num_sms, s);
     if (p.slices == 7) return launch_i8<7>(p, num_sms, s);
     if (p.slices == 8) return launch_i8<8>(p, num_sms, s);
     return cudaErrorInvalidValue;

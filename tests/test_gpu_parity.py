@@ -409,9 +409,9 @@ def test_jk_stream_kernel_all_block_structures(q, monkeypatch):
             assert np.array_equal(vj, vj_r)  # both calls ran the chunked kernel
 
 
-@pytest.mark.parametrize("slices,rel", [(8, 2e-13), (7, 2e-11)])
+@pytest.mark.parametrize("slices,rel", [(8, 2e-13), (7, 1e-12), (6, 1e-10)])
 def test_k3_int8_slices_opt_in(q, slices, rel):
-    """Opt-in K3 on the int8 tensor cores (k3_int8.cu): error-free split of X into 7-bit slices, exact int32 products,
+    """Opt-in K3 on the int8 tensor cores (k3_int8.cu): error-free split of X into 7-bit slices (digits by round to nearest), exact int32 products,
     FP64 recombination.  Against the reference's golden (ij|kl) and against the FP64 K3 of this library, on the
     goldens and on a fragment large enough for many tiles and k chunks; the default (0 slices) is restored."""
     ctx = q.default_context(0)
@@ -446,7 +446,7 @@ def test_k3_int8_slices_opt_in(q, slices, rel):
         ctx.set_k3_int8_slices(0)
 
 
-@pytest.mark.parametrize("slices", [7, 8])
+@pytest.mark.parametrize("slices", [6, 7, 8])
 def test_k3_int8_bit_exact_against_its_restatement(q, slices):
     """The int8-slice K3 is integer work plus a fixed-order FP64 recombination: given the X the device holds
     (qemb_fragment_get_sym after the transform), the numpy restatement oracle/k3_int8_oracle.py must reproduce the

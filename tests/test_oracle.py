@@ -146,16 +146,32 @@ def test_k3_int8_oracle_split_is_error_free_and_within_its_bound():
     X[:, 7] = 0.0                                   # an all-zero pair
     X[3, 11] = 0.75 * 2.0 ** 10                     # exactly representable extremes
     G = X.T @ X
-    for S in (7, 8):
+    for S in (6, 7, 8):
         e, D, R = ko.slice_int8(X, S)
         rec = sum(D[a] * 2.0 ** -(7 * a + 6) for a in range(S)) + R * 2.0 ** -(7 * S - 1)
         assert np.array_equal(np.ldexp(rec, e[None, :]), X)
-        assert all(np.abs(d).max() <= 127 and np.array_equal(d, np.trunc(d)) for d in D) and np.abs(D[0]).max() <= 63
-        assert np.abs(R).max() < 1.0
+        assert all(np.abs(d).max() <= 64 and np.array_equal(d, np.trunc(d)) for d in D)   # round to nearest: 7-bit digits
+        assert np.abs(R).max() <= 0.5
         G8 = ko.gram_int8(X, S)
         assert np.array_equal(G8, G8.T)
         scale = np.ldexp(1.0, e[:, None] + e[None, :])
         err = np.abs(G8 - G) / scale
         assert err.max() <= ko.truncation_bound(naux, S) + 4 * naux * 2.0 ** -53
-        assert np.abs(G8 - G).max() <= (1e-11 if S == 7 else 1e-13) * np.abs(G).max()
-    assert ko.truncation_bound(2716, 7) < 1.5e-10 and ko.truncation_bound(2716, 8) < 1.5e-12  # why 7 slices are not the default
+        assert np.abs(G8 - G).max() <= {6: 1e-10, 7: 1e-12, 8: 1e-14}[S] * np.abs(G).max()
+    # worst case (every rounding error aligned) at the benchmark's naux: why 6 slices stay an explicit choice
+    assert ko.truncation_bound(2716, 6) > 1e-10 > ko.truncation_bound(2716, 7) and ko.truncation_bound(2716, 8) < 1e-12
+
+
+def test_k3_int8_parity_study_quick():
+    """Reduced run of tests/int8_parity_study.py (the full sweep is profiles/k3_int8_parity_study_r1.jsonl): on real
+    fragment operands, for metric condition numbers 1e2 .. 1e10 and for X cut into row slabs, 7 slices stay four
+    orders of magnitude inside the 1e-10 bar and 8 slices at the FP64 product's own rounding level."""
+    import int8_parity_study as st
+
+    rows = st.run(quick=True, out=None)
+    assert len(rows) == 6
+    for r in rows:
+        assert r["exact_vs_longdouble"] <= 1e-15
+        for ns in (1, 4):
+            assert r[f"int8x7_slabs{ns}"] <= 1e-13 and r[f"int8x7_slabs{ns}"] <= r["bound_x_scale_7"]
+            assert r[f"int8x8_slabs{ns}"] <= max(1e-15, 4.0 * r["fp64_vs_exact"])
