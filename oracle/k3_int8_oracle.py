@@ -26,7 +26,8 @@ import numpy as np
 def slice_int8(X: np.ndarray, slices: int):
     """Exponent per column, the integer slices (as float64 arrays holding integers in [-64, 64]) and the remainder
     in units of the last digit (|r| <= 1/2)."""
-    X = np.asarray(X, dtype=np.float64)
+    X = np.array(X, dtype=np.float64)
+    X[:, ~np.isfinite(X).all(axis=0)] = 0.0  # poisoned pairs (NaN / Inf): zero digits; gram_int8 marks them
     m = np.abs(X).max(axis=0) if X.shape[0] else np.zeros(X.shape[1])
     _, e = np.frexp(m)                       # m = f 2^e, f in [0.5, 1); e = 0 for m = 0
     e = np.where(m > 0, e, 0).astype(np.int64)
@@ -53,7 +54,11 @@ def gram_int8(X: np.ndarray, slices: int) -> np.ndarray:
     g = np.zeros((npair, npair))
     for d in range(slices - 1, -1, -1):      # smallest terms first; product exact => same rounding as the kernel's fma
         g = acc[d] * 2.0 ** -(7 * d + 12) + g
-    return np.ldexp(g, e[:, None] + e[None, :])
+    G = np.ldexp(g, e[:, None] + e[None, :])
+    bad = ~np.isfinite(np.asarray(X, dtype=np.float64)).all(axis=0)  # as the FP64 product: row and column poisoned
+    G[bad, :] = np.nan
+    G[:, bad] = np.nan
+    return G
 
 
 def truncation_bound(naux: int, slices: int) -> float:

@@ -30,6 +30,7 @@ constexpr int KC = 128;       // bytes (= int8 elements) of K per stage = one sw
 constexpr int A_RING = 4;
 constexpr int A_BYTES = TM * KC, B_BYTES = TN * KC;
 constexpr int NTHREADS_I8 = 32 * 6;
+constexpr int EXPO_POISON = -(1 << 30); // exponent entry of a pair whose column of X holds a NaN or an Inf
 template <int S>
 constexpr int smem_bytes_i8() { return A_RING * A_BYTES + 2 * S * B_BYTES + 1024; }
 
@@ -83,19 +84,24 @@ __global__ void slice_kernel(const double *X, int64_t ldx, int naux, int naux_pa
     const double *x = X + ldx * j;
     __shared__ double red[32];
     double m = 0.0;
-    for (int p = threadIdx.x; p < naux; p += blockDim.x) m = fmax(m, fabs(x[p]));
+    int bad = 0; // NaN or Inf in this column: the FP64 product would poison row and column j of G, so does this path
+    for (int p = threadIdx.x; p < naux; p += blockDim.x) {
+        const double a = fabs(x[p]);
+        m = fmax(m, a);
+        bad |= !(a <= 1.7976931348623157e308);
+    }
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
-    __syncthreads();
+    bad = __syncthreads_or(bad);
     m = 0.0;
     for (int w = 0; w < (int)(blockDim.x >> 5); ++w) m = fmax(m, red[w]);
     int e = 0;
-    if (m > 0.0) {
+    if (m > 0.0 && !bad) {
         frexp(m, &e); // m = f * 2^e, f in [0.5, 1)  ->  |x| * 2^-e < 1
     }
-    if (threadIdx.x == 0) expo[j] = e;
+    if (threadIdx.x == 0) expo[j] = bad ? EXPO_POISON : e;
     for (int p = threadIdx.x; p < naux_pad; p += blockDim.x) {
-        double r = p < naux ? ldexp(x[p], -e) : 0.0; // exact
+        double r = (p < naux && !bad) ? ldexp(x[p], -e) : 0.0; // exact
         double scale = 64.0;
 #pragma unroll
         for (int a = 0; a < S; ++a) {
@@ -254,7 +260,9 @@ __global__ void __launch_bounds__(NTHREADS_I8, 1) gemm_kernel_i8(const __grid_co
                 for (int q = 0; q < 8; ++q) {
                     const int64_t j = (int64_t)tile.y * TN + c0 + q;
                     if (i < p.npair && j < p.npair && j <= i) {
-                        const double val = ldexp(g[q], ei + p.expo[j]);
+                        const int ej = p.expo[j];
+                        const double val = (ei == EXPO_POISON || ej == EXPO_POISON) ? __longlong_as_double(0x7ff8000000000000ll)
+                                                                                    : ldexp(g[q], ei + ej);
                         p.G[i + p.ldg * j] = val;
                         p.G[j + p.ldg * i] = val;
                     }

@@ -158,6 +158,14 @@ def test_k3_int8_oracle_split_is_error_free_and_within_its_bound():
         err = np.abs(G8 - G) / scale
         assert err.max() <= ko.truncation_bound(naux, S) + 4 * naux * 2.0 ** -53
         assert np.abs(G8 - G).max() <= {6: 1e-10, 7: 1e-12, 8: 1e-14}[S] * np.abs(G).max()
+    # a NaN or an Inf in X poisons row and column of that pair, as the FP64 product would, and nothing else
+    Xb = X.copy()
+    Xb[5, 20], Xb[9, 33] = np.nan, np.inf
+    Gb, G0 = ko.gram_int8(Xb, 7), ko.gram_int8(X, 7)
+    keep = np.ones(npair, bool)
+    keep[[20, 33]] = False
+    assert np.isnan(Gb[~keep, :]).all() and np.isnan(Gb[:, ~keep]).all()
+    assert np.array_equal(Gb[np.ix_(keep, keep)], G0[np.ix_(keep, keep)])
     # worst case (every rounding error aligned) at the benchmark's naux: why 6 slices stay an explicit choice
     assert ko.truncation_bound(2716, 6) > 1e-10 > ko.truncation_bound(2716, 7) and ko.truncation_bound(2716, 8) < 1e-12
 
