@@ -213,8 +213,8 @@ int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
  * error-free split of X into that many 7-bit integer slices (digits by round to nearest) multiplied on the int8 tensor
  * cores with exact int32 accumulation and recombined in FP64 (k3_int8.cu).  Deviation from the exact product on
  * K3-shaped operands, as a fraction of max|G|: about 3e-12 (6), 1e-14 (7), FP64 rounding level (8)
- * (profiles/k3_int8_parity_study_r1.jsonl).  Default: QEMB_K3_INT8 or 0.  The accumulating transform
- * (out_is_device == 2) always uses the FP64 path. */
+ * (profiles/k3_int8_parity_study_r1.jsonl).  Default: QEMB_K3_INT8 or 0.  Applies to the accumulating
+ * transform (out_is_device == 2) as well: every slab is sliced with its own exponents and its lower triangle added. */
 int qemb_ctx_set_k3_int8_slices(qemb_ctx *ctx, int slices);
 /* number of host worker threads of the library (QEMB_HOST_THREADS, default: cores in the affinity mask - 1) */
 int qemb_host_threads(int *n);

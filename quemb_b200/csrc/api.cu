@@ -1532,9 +1532,9 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         CU(cudaEventRecord(w->ev[3], cs));
         w->ev_valid[3] = true;
     }
-    // opt-in int8-slice K3 (k3_int8.cu); the accumulating form stays FP64, and so do slabs deep enough to overflow the
-    // exact int32 sums (digits in [-64, 64], at most `slices` digit pairs per order: slices * rows * 64^2 < 2^31)
-    if (w->ctx->k3_slices && !accumulate && (int64_t)w->ctx->k3_slices * w->mrows * 4096 < (int64_t)2147483647) {
+    // opt-in int8-slice K3 (k3_int8.cu), plain and accumulating; slabs deep enough to overflow the exact int32 sums stay
+    // FP64 (digits in [-64, 64], at most `slices` digit pairs per order: slices * rows * 64^2 < 2^31)
+    if (w->ctx->k3_slices && (int64_t)w->ctx->k3_slices * w->mrows * 4096 < (int64_t)2147483647) {
         GramI8Params q;
         q.X = p.X;
         q.ldx = p.ldx;
@@ -1543,6 +1543,7 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         q.G = dst;
         q.ldg = ld;
         q.slices = w->ctx->k3_slices;
+        q.accumulate = accumulate;
         TRY(w->gram_i8.reserve(gram_i8_scratch_bytes(q.nrows, q.npair, q.slices)));
         q.scratch = w->gram_i8.as<int8_t>();
         CU(launch_gram_int8(q, w->ctx->num_sms, cs));

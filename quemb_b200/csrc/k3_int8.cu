@@ -123,6 +123,7 @@ struct GemmParams {
     int64_t ldg;
     const int2 *tiles;        // (I, J): A tile rows 128 I .., B tile rows 64 J ..; lower triangle incl. diagonal blocks
     int ntiles;
+    int accumulate;           // 1: add the lower triangle into G (possibly peer memory), no mirror
 };
 
 template <int S>
@@ -263,8 +264,12 @@ __global__ void __launch_bounds__(NTHREADS_I8, 1) gemm_kernel_i8(const __grid_co
                         const int ej = p.expo[j];
                         const double val = (ei == EXPO_POISON || ej == EXPO_POISON) ? __longlong_as_double(0x7ff8000000000000ll)
                                                                                     : ldexp(g[q], ei + ej);
-                        p.G[i + p.ldg * j] = val;
-                        p.G[j + p.ldg * i] = val;
+                        if (p.accumulate) {
+                            atomicAdd_system(&p.G[i + p.ldg * j], val);
+                        } else {
+                            p.G[i + p.ldg * j] = val;
+                            p.G[j + p.ldg * i] = val;
+                        }
                     }
                 }
             }
@@ -334,7 +339,7 @@ cudaError_t launch_i8(const GramI8Params &p, int num_sms, cudaStream_t s)
     i8_tiles_kernel<<<(nI + 127) / 128, 128, 0, s>>>(tiles, nI, nJ);
     cudaError_t e = cudaFuncSetAttribute(gemm_kernel_i8<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes_i8<S>());
     if (e != cudaSuccess) return e;
-    GemmParams gp{p.npair, naux_pad / KC, naux_pad, expo, p.G, p.ldg, tiles, ntiles};
+    GemmParams gp{p.npair, naux_pad / KC, naux_pad, expo, p.G, p.ldg, tiles, ntiles, p.accumulate};
     const int grid = ntiles < num_sms ? ntiles : num_sms;
     gemm_kernel_i8<S><<<grid, NTHREADS_I8, smem_bytes_i8<S>(), s>>>(maps[0], maps[1], gp);
     return cudaGetLastError();

@@ -36,7 +36,9 @@ struct GramI8Params {
     int64_t npair;
     double *G;         // npair x npair, ld = ldg (both triangles written)
     int64_t ldg;
-    int slices;        // 7 (1e-12 of max|G|) or 8 (1e-14)
+    int slices;        // 6, 7 or 8 (about 3e-12 / 1e-14 / FP64 rounding level of max|G|)
+    int accumulate = 0; // 1: the lower triangle is ADDED into G (system-scope red.add.f64; G may be a peer GPU's memory),
+                        //    nothing is mirrored -- same contract as GramParams::accumulate of the FP64 kernel
     int8_t *scratch;   // gram_i8_scratch_bytes(...) bytes, 256-byte aligned
 };
 int gram_i8_naux_pad(int nrows);

@@ -525,6 +525,12 @@ def test_fused_peer_accumulate_two_gpus(q):
 def test_accumulate_mode_and_device_mirror_single_gpu(q):
     """out_is_device = 2 on one device: two slabs accumulated into one zeroed matrix + device mirror = the oracle's
     (ij|kl); exercises the red.add epilogue, qemb_device_zero / _mirror_lower / _to_host and the IPC allocator."""
+    G, G_oracle = _accumulate_two_slabs(q)
+    assert np.array_equal(G, G.T)
+    assert np.abs(G - G_oracle).max() <= TOL
+
+
+def _accumulate_two_slabs(q):
     import ctypes
 
     from quemb_b200._lib import c_dbl, c_i64, c_int, c_p, check, lib, ptr
@@ -552,8 +558,7 @@ def test_accumulate_mode_and_device_mirror_single_gpu(q):
     G = np.empty((npair, npair), order="F")
     check(lib().qemb_device_to_host(ctx._h, ptr(G), dev, c_i64(8 * npair * npair)))
     check(lib().qemb_ipc_free(ctx._h, dev))
-    assert np.array_equal(G, G.T)
-    assert np.abs(G - _oracle_G(p, TA)).max() <= TOL
+    return G, _oracle_G(p, TA)
 
 
 def test_hybrid_output_transfer_matches_full_square(q):
@@ -671,3 +676,20 @@ def test_k3_int8_poisoned_pairs_like_the_fp64_product(q):
     assert np.array_equal(np.isnan(G8), np.isnan(G64))
     ok = ~np.isnan(G64)
     assert np.abs(G8[ok] - G64[ok]).max(initial=0.0) <= 1e-12 * max(1.0, np.abs(G64[ok]).max(initial=0.0))
+
+
+@pytest.mark.parametrize("slices,tol", [(8, 1e-13), (7, 1e-12)])
+def test_k3_int8_accumulating_slabs(q, slices, tol):
+    """out_is_device = 2 with the int8-slice K3: each row slab is sliced with its own exponents and its lower triangle
+    added into the shared matrix (what the fused aux-sharded build does over NVLink); the sum stays at the accuracy
+    of a single int8 product (host study: profiles/k3_int8_parity_study_r1.txt, slab columns)."""
+    ctx = q.default_context()
+    G64, G_oracle = _accumulate_two_slabs(q)
+    try:
+        ctx.set_k3_int8_slices(slices)
+        G, _ = _accumulate_two_slabs(q)
+    finally:
+        ctx.set_k3_int8_slices(0)
+    assert np.array_equal(G, G.T)
+    assert np.abs(G - G64).max() <= tol * max(1.0, np.abs(G64).max())
+    assert np.abs(G - G_oracle).max() <= TOL
