@@ -5,7 +5,7 @@ holds (tests/test_gpu_parity.py::test_k3_int8_bit_exact_against_its_restatement)
 against the FP64 product can be studied on the host: this script sweeps the metric condition number, the geometry
 family and the row-slab (aux-sharded / accumulating) decomposition, and writes one JSON line per case.
 
-    python tests/int8_parity_study.py > profiles/k3_int8_parity_study_r1.jsonl
+    python tests/int8_parity_study.py > profiles/k3_int8_parity_study_r1.jsonl      (then --extra, --bench-workload: appended)
 
 "Exact" is the 10-slice restatement (truncation below naux * 2^-68 of the column scales, then FP64 rounding of the
 sum), cross-checked against long double on a sample of entries.
@@ -117,8 +117,29 @@ def run_extra(out=sys.stdout) -> list[dict]:
     return rows
 
 
+def run_bench_workload(out=sys.stdout, frags=(31, 15), nsel: int = 1500) -> list[dict]:
+    """Operands of the benchmark workload itself (C32H66-like, naux 2716): per fragment the `nsel` pairs with the
+    largest columns of X plus `nsel` random ones (the error of an entry depends on its two columns only)."""
+    p = sy.c32h66_like(n_frag=32)
+    rng = np.random.default_rng(20261106)
+    rows = []
+    for f in frags:
+        X = fragment_X(p, f)
+        big = np.argsort(-np.abs(X).max(axis=0))[:nsel]
+        rest = np.setdiff1d(np.arange(X.shape[1]), big)
+        sel = np.sort(np.concatenate([big, rng.choice(rest, nsel, replace=False)]))
+        name = (f"C32H66-like (bench workload) frag {f} (nmo {p.TAs[f].shape[1]}), naux {p.naux}, {2 * nsel} of {X.shape[1]} "
+                f"pairs: the {nsel} largest columns + {nsel} random")
+        rows.append(study_case(name, np.asfortranarray(X[:, sel]), rng, slabs=(1,), slices=(6, 7, 8)))
+        if out is not None:
+            print(json.dumps(rows[-1]), file=out, flush=True)
+    return rows
+
+
 if __name__ == "__main__":
     if "--extra" in sys.argv:
         run_extra()
+    elif "--bench-workload" in sys.argv:
+        run_bench_workload()
     else:
         run(quick="--quick" in sys.argv)
