@@ -466,7 +466,7 @@ def main() -> None:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c32h66", choices=["c32h66", "octane", "tiny"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--k3-int8", type=int, default=0, choices=[0, 6, 7, 8],
+    ap.add_argument("--k3-int8", type=int, default=0, choices=[0, 5, 6, 7, 8],
                     help="opt-in K3 on the int8 tensor cores with that many slices (default 0: FP64 tensor path)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

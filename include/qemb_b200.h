@@ -209,13 +209,18 @@ int qemb_ctx_set_output_mode(qemb_ctx *, int mode);
  * pure triangle transfer) to the copy engine, which has slack while the kernels run. */
 int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
 
-/* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 6, 7 or 8 =
- * error-free split of X into that many 7-bit integer slices (digits by round to nearest) multiplied on the int8 tensor
- * cores with exact int32 accumulation and recombined in FP64 (k3_int8.cu).  Deviation from the exact product on
- * K3-shaped operands, as a fraction of max|G|: about 3e-12 (6), 1e-14 (7), FP64 rounding level (8)
- * (profiles/k3_int8_parity_study_r1.jsonl).  Default: QEMB_K3_INT8 or 0.  Applies to the accumulating
- * transform (out_is_device == 2) as well: every slab is sliced with its own exponents and its lower triangle added. */
+/* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 5 .. 8 = error-free
+ * split of X into that many 8-bit integer slices (balanced base-256 digits of each column rounded below its exponent)
+ * multiplied on the int8 tensor cores with exact int32 accumulation and recombined in FP64 (k3_int8.cu).  Deviation
+ * from the exact product on K3-shaped operands, as a fraction of max|G|: about 1e-11 (5), 2e-13 (6), FP64 rounding
+ * level (7, 8) (profiles/k3_int8_parity_study_r1.txt); cost ~ slices (slices + 1) / 2 int8 products.  Default:
+ * QEMB_K3_INT8 or 0.  Applies to the accumulating transform (out_is_device == 2) as well: every slab is sliced with its
+ * own exponents and its lower triangle added.  Slabs of more than 2^17 / slices rows stay on the FP64 path (int32). */
 int qemb_ctx_set_k3_int8_slices(qemb_ctx *ctx, int slices);
+/* Host twin of the device slicer of the int8 K3 (same source: csrc/k3_int8_digits.h): exponent per column
+ * (expo[c]; a column holding NaN / Inf gets the poison value -2^30 and zero digits) and the digits
+ * D[(c * slices + a) * nrows + p].  Test hook for the CPU suite; no reference counterpart, not on the product path. */
+int qemb_k3_int8_slice_host(const double *X, int64_t ldx, int64_t nrows, int64_t ncols, int slices, int8_t *D, int *expo);
 /* number of host worker threads of the library (QEMB_HOST_THREADS, default: cores in the affinity mask - 1) */
 int qemb_host_threads(int *n);
 /* G[c + ld*r] = G[r + ld*c] for all r > c of an n x n host matrix (the host half of output mode 1; also the

@@ -78,7 +78,7 @@ struct qemb_ctx {
     // mode 1 only: the last `full_frac` of the columns cross PCIe whole (rows 0..n) and are not mirrored on the host:
     // balances the copy engine (slack) against the host threads (the bottleneck of a pure triangle transfer)
     double full_frac = 0.0;
-    // 0: K3 on the FP64 tensor path (default, the parity reference); 6 / 7 / 8: opt-in int8-slice K3 (k3_int8.cu)
+    // 0: K3 on the FP64 tensor path (default, the parity reference); 5 .. 8: opt-in int8-slice K3 (k3_int8.cu)
     int k3_slices = 0;
     int num_sms = 148;
     int64_t h2d_bytes = 0, d2h_bytes = 0; // bytes handed to the copy engines (uploads / G transfers)
@@ -375,7 +375,7 @@ extern "C" int qemb_ctx_create(int device, qemb_ctx **out)
     if (const char *e = std::getenv("QEMB_FULL_COLUMN_FRACTION")) c->full_frac = std::min(1.0, std::max(0.0, std::atof(e)));
     if (const char *e = std::getenv("QEMB_K3_INT8")) {
         const int n = std::atoi(e);
-        c->k3_slices = (n >= 6 && n <= 8) ? n : 0;
+        c->k3_slices = (n >= 5 && n <= 8) ? n : 0;
     }
     CU(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->prep, cudaStreamNonBlocking));
@@ -448,7 +448,7 @@ extern "C" int qemb_ctx_set_full_column_fraction(qemb_ctx *c, double frac)
 
 extern "C" int qemb_ctx_set_k3_int8_slices(qemb_ctx *c, int slices)
 {
-    REQ(c && (slices == 0 || (slices >= 6 && slices <= 8)), "slices must be 0 (FP64 K3), 6, 7 or 8");
+    REQ(c && (slices == 0 || (slices >= 5 && slices <= 8)), "slices must be 0 (FP64 K3) or 5 .. 8");
     c->k3_slices = slices;
     return QEMB_OK;
 }
@@ -1533,8 +1533,8 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         w->ev_valid[3] = true;
     }
     // opt-in int8-slice K3 (k3_int8.cu), plain and accumulating; slabs deep enough to overflow the exact int32 sums stay
-    // FP64 (digits in [-64, 64], at most `slices` digit pairs per order: slices * rows * 64^2 < 2^31)
-    if (w->ctx->k3_slices && (int64_t)w->ctx->k3_slices * w->mrows * 4096 < (int64_t)2147483647) {
+    // FP64 (digits in [-128, 127], at most `slices` digit pairs per order: slices * rows * 128^2 < 2^31)
+    if (w->ctx->k3_slices && (int64_t)w->ctx->k3_slices * w->mrows * 16384 < (int64_t)2147483647) {
         GramI8Params q;
         q.X = p.X;
         q.ldx = p.ldx;

@@ -1,12 +1,14 @@
-// k3_int8.cu -- OPT-IN K3 (G = X^T X) through 7-bit integer slices on the int8 tensor cores (tcgen05.mma kind::i8,
-// SASS UTCIMMA, int32 accumulators in TMEM); off by default (qemb_ctx_set_k3_int8_slices / QEMB_K3_INT8 = 6, 7 or 8).
+// k3_int8.cu -- OPT-IN K3 (G = X^T X) through 8-bit integer slices on the int8 tensor cores (tcgen05.mma kind::i8,
+// SASS UTCIMMA, int32 accumulators in TMEM); off by default (qemb_ctx_set_k3_int8_slices / QEMB_K3_INT8 = 5 .. 8).
 //
 // Same result as k3_gram.cu (reference: G = X^T X in FP64, cpp:620) up to the dropped slices:
-//   X[:, j] = 2^e_j * sum_{a<S} 2^-(7a+6) D_a[:, j]  (+ remainder <= 2^-7S),  D_a int8 in [-64, 64] (digits by round to
-//             nearest: the split is error free and the dropped terms carry no sign bias)
-//   G_ij    = 2^(e_i+e_j) * sum_{d<S} 2^-(7d+12) * sum_{a+b=d} <D_a[:, i], D_b[:, j]>     (inner sums exact in int32)
-// measured on K3-shaped operands: S = 7 -> 1.3e-12 of max|G|, S = 8 -> 1.1e-14 (profiles/k3_i8_proto_r1.txt), at
-// 1.9x / 1.3x the speed of the FP64 tensor peak.  The FP64 DMMA kernel stays the default and the parity reference.
+//   X[:, j] = 2^e_j * ( sum_{a<S} 2^-(8a+6) D_a[:, j] + R ),  |R| <= 2^-(8S-1),  D_a int8: balanced base-256 digits of the
+//             column rounded to 8S-2 bits below its exponent (k3_int8_digits.h); the split is error free
+//   G_ij    = 2^(e_i+e_j) * sum_{d<S} 2^-(8d+12) * sum_{a+b=d} <D_a[:, i], D_b[:, j]>     (inner sums exact in int32)
+// History: round 1 measured a truncating base-128 slicer on the GPU (S = 7 -> 1.3e-12 of max|G| at 1.9x the FP64 tensor
+// peak, S = 8 -> 1.1e-14 at 1.3x; profiles/k3_i8_proto_r1.txt); rounded, balanced base-256 digits give more per slice
+// product: S = 6 -> 2e-13, S = 7 -> 3e-16 on the same operands (profiles/k3_int8_parity_study_r1.txt).
+// The FP64 DMMA kernel stays the default and the parity reference.
 //
 // slice_kernel : one CTA per column of X -> exponent e_j and the S slices, K-major per pair:
 //                D[pair][a * naux_pad + P]  (one row of S * naux_pad bytes per pair, pad pairs zero)
@@ -18,6 +20,7 @@
 //                           every slice tile loaded once serves up to S products
 //                  warps 2-5 epilogue: tcgen05.ld of the S accumulators, FP64 recombination, scaling, store + mirror
 #include "common.cuh"
+#include "k3_int8_digits.h"
 #include "kernels.cuh"
 #include <cuda.h>
 
@@ -100,17 +103,7 @@ __global__ void slice_kernel(const double *X, int64_t ldx, int naux, int naux_pa
         frexp(m, &e); // m = f * 2^e, f in [0.5, 1)  ->  |x| * 2^-e < 1
     }
     if (threadIdx.x == 0) expo[j] = bad ? EXPO_POISON : e;
-    for (int p = threadIdx.x; p < naux_pad; p += blockDim.x) {
-        double r = (p < naux && !bad) ? ldexp(x[p], -e) : 0.0; // exact
-        double scale = 64.0;
-#pragma unroll
-        for (int a = 0; a < S; ++a) {
-            const double t = rint(r * scale); // nearest, ties to even: digits in [-64, 64], no sign bias in the dropped terms
-            r = r * scale - t; // exact
-            row[a * naux_pad + p] = (int8_t)t;
-            scale = 128.0;
-        }
-    }
+    for (int p = threadIdx.x; p < naux_pad; p += blockDim.x) i8_digits<S>((p < naux && !bad) ? x[p] : 0.0, e, row + p, naux_pad);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -253,7 +246,7 @@ __global__ void __launch_bounds__(NTHREADS_I8, 1) gemm_kernel_i8(const __grid_co
                 for (int q = 0; q < 8; ++q) g[q] = 0.0;
 #pragma unroll
                 for (int d = S - 1; d >= 0; --d) { // small terms first
-                    const double w = ldexp(1.0, -(7 * d + 12));
+                    const double w = ldexp(1.0, -(8 * d + 12));
 #pragma unroll
                     for (int q = 0; q < 8; ++q) g[q] = fma((double)(int32_t)v[d][q], w, g[q]);
                 }
@@ -358,6 +351,7 @@ size_t gram_i8_scratch_bytes(int nrows, int64_t npair, int slices)
 cudaError_t launch_gram_int8(const GramI8Params &p, int num_sms, cudaStream_t s)
 {
     if (p.npair <= 0) return cudaSuccess;
+    if (p.slices == 5) return launch_i8<5>(p, num_sms, s);
     if (p.slices == 6) return launch_i8<6>(p, num_sms, s);
     if (p.slices == 7) return launch_i8<7>(p, num_sms, s);
     if (p.slices == 8) return launch_i8<8>(p, num_sms, s);
@@ -365,3 +359,34 @@ cudaError_t launch_gram_int8(const GramI8Params &p, int num_sms, cudaStream_t s)
 }
 
 } // namespace qemb
+
+// Host twin of slice_kernel (same exponent rule, same digit routine): D[(c * slices + a) * nrows + p], expo[c].
+// For the CPU test suite (the device slicer against oracle/k3_int8_oracle.py without a GPU); not on the product path.
+extern "C" int qemb_k3_int8_slice_host(const double *X, int64_t ldx, int64_t nrows, int64_t ncols, int slices, int8_t *D, int *expo)
+{
+    if (!X || !D || !expo || nrows < 0 || ncols < 0 || ldx < nrows || slices < 5 || slices > 8) return 1;
+    for (int64_t c = 0; c < ncols; ++c) {
+        const double *x = X + ldx * c;
+        double m = 0.0;
+        bool bad = false;
+        for (int64_t p = 0; p < nrows; ++p) {
+            const double a = fabs(x[p]);
+            m = fmax(m, a);
+            bad |= !(a <= 1.7976931348623157e308);
+        }
+        int e = 0;
+        if (m > 0.0 && !bad) frexp(m, &e);
+        expo[c] = bad ? qemb::EXPO_POISON : e;
+        int8_t *row = D + c * slices * nrows;
+        for (int64_t p = 0; p < nrows; ++p) {
+            const double v = bad ? 0.0 : x[p];
+            switch (slices) {
+            case 5: qemb::i8_digits<5>(v, e, row + p, nrows); break;
+            case 6: qemb::i8_digits<6>(v, e, row + p, nrows); break;
+            case 7: qemb::i8_digits<7>(v, e, row + p, nrows); break;
+            default: qemb::i8_digits<8>(v, e, row + p, nrows); break;
+            }
+        }
+    }
+    return 0;
+}

@@ -87,9 +87,9 @@ class Context:
         check(lib().qemb_ctx_set_full_column_fraction(self._h, c_dbl(frac)))
 
     def set_k3_int8_slices(self, slices: int) -> None:
-        """Opt-in K3 on the int8 tensor cores (0 = FP64 path, the default and the parity reference; 6, 7 or 8
-        integer slices with digits by round to nearest: about 3e-12 / 1e-14 / FP64 rounding level of max|(ij|kl)| from
-        the exact product; 7 and 8 slices measured at 1.9x / 1.3x the FP64 tensor peak)."""
+        """Opt-in K3 on the int8 tensor cores (0 = FP64 path, the default and the parity reference; 5 .. 8 integer
+        slices of 8 bits: about 1e-11 / 2e-13 / FP64 rounding level (7, 8) of max|(ij|kl)| from the exact product, cost
+        ~ slices (slices + 1) / 2; see ``profiles/k3_int8_parity_study_r1.txt``)."""
         check(lib().qemb_ctx_set_k3_int8_slices(self._h, c_int(slices)))
 
     def set_timing(self, enabled: bool) -> None:

@@ -586,11 +586,12 @@ def test_hybrid_output_transfer_matches_full_square(q):
         assert np.array_equal(G, G0)
 
 
-# int8-slice K3 (opt-in): kept last in the file -- rint slicing, 6 slices and the NaN rule were added after the
-# round-1 GPU minutes were spent and were checked through the restatement only
-@pytest.mark.parametrize("slices,rel", [(8, 2e-13), (7, 1e-12), (6, 1e-10)])
+# int8-slice K3 (opt-in): kept last in the file -- the rounded base-256 slicer, 5 / 6 slices, the NaN rule and the
+# accumulating form were made after the round-1 GPU minutes were spent and were checked on the host only (restatement,
+# host twin of the device slicer)
+@pytest.mark.parametrize("slices,rel", [(8, 2e-13), (7, 2e-13), (6, 1e-11), (5, 1e-9)])
 def test_k3_int8_slices_opt_in(q, slices, rel):
-    """Opt-in K3 on the int8 tensor cores (k3_int8.cu): error-free split of X into 7-bit slices (digits by round to nearest), exact int32 products,
+    """Opt-in K3 on the int8 tensor cores (k3_int8.cu): error-free split of X into 8-bit slices (balanced digits of the rounded column), exact int32 products,
     FP64 recombination.  Against the reference's golden (ij|kl) and against the FP64 K3 of this library, on the
     goldens and on a fragment large enough for many tiles and k chunks; the default (0 slices) is restored."""
     ctx = q.default_context(0)
@@ -625,7 +626,7 @@ def test_k3_int8_slices_opt_in(q, slices, rel):
         ctx.set_k3_int8_slices(0)
 
 
-@pytest.mark.parametrize("slices", [6, 7, 8])
+@pytest.mark.parametrize("slices", [5, 6, 7, 8])
 def test_k3_int8_bit_exact_against_its_restatement(q, slices):
     """The int8-slice K3 is integer work plus a fixed-order FP64 recombination: given the X the device holds
     (qemb_fragment_get_sym after the transform), the numpy restatement oracle/k3_int8_oracle.py must reproduce the
@@ -678,7 +679,7 @@ def test_k3_int8_poisoned_pairs_like_the_fp64_product(q):
     assert np.abs(G8[ok] - G64[ok]).max(initial=0.0) <= 1e-12 * max(1.0, np.abs(G64[ok]).max(initial=0.0))
 
 
-@pytest.mark.parametrize("slices,tol", [(8, 1e-13), (7, 1e-12)])
+@pytest.mark.parametrize("slices,tol", [(7, 1e-13), (6, 1e-11)])
 def test_k3_int8_accumulating_slabs(q, slices, tol):
     """out_is_device = 2 with the int8-slice K3: each row slab is sliced with its own exponents and its lower triangle
     added into the shared matrix (what the fused aux-sharded build does over NVLink); the sum stays at the accuracy

@@ -134,6 +134,18 @@ def test_consumer_oracle_identity():
     assert np.abs(e2 - np.einsum("ij,ij->i", D[:n_frag], 2 * vj[:n_frag] - vk[:n_frag])).max() <= 1e-12
 
 
+def _int8_test_operand(rng, naux=300, npair=90):
+    X = rng.standard_normal((naux, npair)) * np.exp(-6 * rng.random(npair))[None, :] * np.exp(-4 * rng.random(naux))[:, None]
+    X[:, 7] = 0.0                                   # an all-zero pair
+    X[3, 11] = 0.75 * 2.0 ** 10                     # exactly representable extremes
+    X[:, 13] = -np.abs(X[:, 13])                    # a one-signed column
+    X[:, 17] *= 1e-300                              # scaled into the subnormal range (some entries underflow)
+    X[5:40, 19] = (np.arange(35) - 17 + 0.5) * 2.0 ** -46  # exact ties of the 6-slice rounding (column maximum 0.75)
+    X[0, 19], X[1:5, 19], X[40:, 19] = 0.75, 0.0, 0.0
+    X[:, 23] = 1.0 - 2.0 ** -53                     # largest r below 1: N reaches 2^(8S-2)
+    return X
+
+
 def test_k3_int8_oracle_split_is_error_free_and_within_its_bound():
     """The restatement of the opt-in int8-slice K3: the split reconstructs X exactly (slices + remainder), the
     integer sums stay inside int32, and the recombined matrix is within the worst-case truncation bound of the FP64
@@ -142,22 +154,25 @@ def test_k3_int8_oracle_split_is_error_free_and_within_its_bound():
 
     rng = np.random.default_rng(5)
     naux, npair = 300, 90
-    X = rng.standard_normal((naux, npair)) * np.exp(-6 * rng.random(npair))[None, :] * np.exp(-4 * rng.random(naux))[:, None]
-    X[:, 7] = 0.0                                   # an all-zero pair
-    X[3, 11] = 0.75 * 2.0 ** 10                     # exactly representable extremes
+    X = _int8_test_operand(rng, naux, npair)
     G = X.T @ X
-    for S in (6, 7, 8):
+    for S in (5, 6, 7, 8):
         e, D, R = ko.slice_int8(X, S)
-        rec = sum(D[a] * 2.0 ** -(7 * a + 6) for a in range(S)) + R * 2.0 ** -(7 * S - 1)
+        N = np.zeros(X.shape, dtype=np.int64)
+        for a in range(S):                           # the digits are those of one integer, N = rint(r 2^(8S-2)) ...
+            N = N * 256 + D[a].astype(np.int64)
+        rec = np.ldexp(N.astype(np.float64), -(8 * S - 2)) + R   # ... and N 2^-(8S-2) + R gives r back exactly
         assert np.array_equal(np.ldexp(rec, e[None, :]), X)
-        assert all(np.abs(d).max() <= 64 and np.array_equal(d, np.trunc(d)) for d in D)   # round to nearest: 7-bit digits
-        assert np.abs(R).max() <= 0.5
+        assert all(d.min() >= -128 and d.max() <= 127 and np.array_equal(d, np.trunc(d)) for d in D)
+        assert np.abs(D[0]).max() <= 65
+        assert np.abs(R).max() <= 2.0 ** -(8 * S - 1)
         G8 = ko.gram_int8(X, S)
         assert np.array_equal(G8, G8.T)
         scale = np.ldexp(1.0, e[:, None] + e[None, :])
-        err = np.abs(G8 - G) / scale
-        assert err.max() <= ko.truncation_bound(naux, S) + 4 * naux * 2.0 ** -53
-        assert np.abs(G8 - G).max() <= {6: 1e-10, 7: 1e-12, 8: 1e-14}[S] * np.abs(G).max()
+        ok = scale > 0                               # 2^(e_i+e_j) underflows for the subnormal column: G is 0 there
+        assert np.array_equal(G8[~ok], G[~ok])
+        assert (np.abs(G8 - G)[ok] / scale[ok]).max() <= ko.truncation_bound(naux, S) + 4 * naux * 2.0 ** -53
+        assert np.abs(G8 - G).max() <= {5: 1e-9, 6: 1e-11, 7: 1e-14, 8: 1e-14}[S] * np.abs(G).max()
     # a NaN or an Inf in X poisons row and column of that pair, as the FP64 product would, and nothing else
     Xb = X.copy()
     Xb[5, 20], Xb[9, 33] = np.nan, np.inf
@@ -166,14 +181,42 @@ def test_k3_int8_oracle_split_is_error_free_and_within_its_bound():
     keep[[20, 33]] = False
     assert np.isnan(Gb[~keep, :]).all() and np.isnan(Gb[:, ~keep]).all()
     assert np.array_equal(Gb[np.ix_(keep, keep)], G0[np.ix_(keep, keep)])
-    # worst case (every rounding error aligned) at the benchmark's naux: why 6 slices stay an explicit choice
-    assert ko.truncation_bound(2716, 6) > 1e-10 > ko.truncation_bound(2716, 7) and ko.truncation_bound(2716, 8) < 1e-12
+    # worst case (every rounding error aligned) at the benchmark's naux, per unit of 2^(e_i+e_j)
+    assert 1e-9 > ko.truncation_bound(2716, 6) > 1e-10 > 2e-12 > ko.truncation_bound(2716, 7) and ko.truncation_bound(2716, 8) < 1e-14
+
+
+def test_k3_int8_device_slicer_source_matches_the_restatement():
+    """qemb_k3_int8_slice_host runs the digit routine the device slicer runs (csrc/k3_int8_digits.h, one source for
+    host and device) under the same exponent rule: its exponents and digits must equal the restatement's bit for bit,
+    including zero columns, subnormals, exact ties, N = 2^(8S-2) and NaN / Inf columns."""
+    import ctypes
+
+    from oracle import k3_int8_oracle as ko
+    from quemb_b200._lib import lib
+
+    rng = np.random.default_rng(6)
+    X = np.asfortranarray(_int8_test_operand(rng))
+    X[5, 20], X[9, 33] = np.nan, -np.inf
+    naux, npair = X.shape
+    fn = lib().qemb_k3_int8_slice_host
+    for S in (5, 6, 7, 8):
+        D = np.zeros((npair, S, naux), dtype=np.int8)
+        expo = np.zeros(npair, dtype=np.int32)
+        rc = fn(X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(naux), ctypes.c_int64(naux), ctypes.c_int64(npair),
+                ctypes.c_int(S), D.ctypes.data_as(ctypes.c_void_p), expo.ctypes.data_as(ctypes.c_void_p))
+        assert rc == 0
+        e, Dr, _ = ko.slice_int8(X, S)
+        bad = ~np.isfinite(X).all(axis=0)
+        assert np.array_equal(expo[~bad], e[~bad]) and (expo[bad] == ko.EXPO_POISON).all() and bad.sum() == 2
+        for a in range(S):
+            assert np.array_equal(D[:, a, :].T.astype(np.float64), Dr[a]), (S, a)
 
 
 def test_k3_int8_parity_study_quick():
     """Reduced run of tests/int8_parity_study.py (the full sweep is profiles/k3_int8_parity_study_r1.jsonl): on real
-    fragment operands, for metric condition numbers 1e2 .. 1e10 and for X cut into row slabs, 7 slices stay four
-    orders of magnitude inside the 1e-10 bar and 8 slices at the FP64 product's own rounding level."""
+    fragment operands, for metric condition numbers 1e2 .. 1e10 and for X cut into row slabs, 6 slices stay two
+    orders of magnitude inside the 1e-10 bar, 7 slices at the FP64 product's own rounding level, and the 8-slice
+    result agrees with long double to 1e-15."""
     import int8_parity_study as st
 
     rows = st.run(quick=True, out=None)
@@ -181,5 +224,5 @@ def test_k3_int8_parity_study_quick():
     for r in rows:
         assert r["exact_vs_longdouble"] <= 1e-15
         for ns in (1, 4):
-            assert r[f"int8x7_slabs{ns}"] <= 1e-13 and r[f"int8x7_slabs{ns}"] <= r["bound_x_scale_7"]
-            assert r[f"int8x8_slabs{ns}"] <= max(1e-15, 4.0 * r["fp64_vs_exact"])
+            assert r[f"int8x6_slabs{ns}"] <= 1e-12 and r[f"int8x6_slabs{ns}"] <= r["bound_x_scale_6"]
+            assert r[f"int8x7_slabs{ns}"] <= max(1e-15, 4.0 * r["fp64_vs_exact"])
