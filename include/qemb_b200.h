@@ -45,6 +45,11 @@ typedef struct qemb_workspace qemb_workspace; /* per-caller scratch: plan, B, X,
 
 const char *qemb_last_error(void);
 const char *qemb_version(void);
+/* get_log_level / set_log_level, hpp:34-46 / pyi:139-157: process-global, Python logging levels (default 40 = Error).
+ * At <= 20 (Info) qemb_fragment_transform prints the reference's "[TIMER] <step> finished in <t> s" lines (hpp:170-204)
+ * from CUDA-event times of screening, K1, K2a, K2b and K3; reading them waits for the fragment. */
+int qemb_get_log_level(void);
+int qemb_set_log_level(int level);
 
 /* -- device -------------------------------------------------------------------------------------- */
 int qemb_device_count(int *n);
@@ -79,12 +84,19 @@ int qemb_tensor_column(const qemb_tensor *, int64_t mu, int64_t nu, int64_t *col
  * (a pair whose key was never assigned reads column 0, the reference's operator[] default). */
 int qemb_tensor_reachable_columns(const qemb_tensor *, int64_t *col /* nnz(exch) */);
 /* fills columns [col0, col0+ncols) from host (replaces writes through mut_unique_dense_data,
- * cpp:810-812, py:486-488) */
+ * cpp:810-812, py:486-488).  A whitened tensor accepts only a full replacement (which clears the flag): a partial
+ * refresh would mix raw and L^-1-scaled columns -- QEMB_EINVAL; clear the flag with qemb_tensor_set_whitened first. */
 int qemb_tensor_upload(qemb_tensor *, const double *host, int64_t ld_host, int64_t col0, int64_t ncols);
 /* Staging of one libcint block (replaces the Python triple loop py:459-488):
  * block[(i * n_j + j) * naux + P] = (P | p0+i, q0+j), C order as `_aux_e2(...)` returns it; every screened pair
  * with q0+j <= p0+i receives its column on the device, all other entries of the block are ignored. */
 int qemb_tensor_scatter_block(qemb_tensor *, const double *block, int64_t n_i, int64_t n_j, int64_t p0, int64_t q0);
+/* (asynchronous: `block` is copied into one of two pinned staging slots before the call returns, the H2D copy and the
+ * scatter kernel of block b overlap the caller's evaluation of block b+1; any later read of the tensor is ordered
+ * behind them on the compute stream) */
+/* number of NaN entries left in the tensor: a column nobody filled keeps the NaN of qemb_tensor_create (cpp:160); the
+ * reference asserts `not np.isnan(result.unique_dense_data).any()` at the end of get_sparse_P_mu_nu (py:492) */
+int qemb_tensor_count_nan(qemb_tensor *, int64_t *n);
 /* reads columns back (unique_dense_data / __getitem__, cpp:203-215, 806-826) */
 int qemb_tensor_download(const qemb_tensor *, double *host, int64_t ld_host, int64_t col0, int64_t ncols);
 
@@ -188,10 +200,18 @@ int qemb_fragment_transform(qemb_workspace *, const qemb_tensor *, const qemb_me
  * D, vj, vk: nmo x nmo column-major host matrices; D must be symmetric.  Synchronous. */
 int qemb_fragment_jk(qemb_workspace *, const double *D_host, int64_t ldd, double *vj_host, double *vk_host,
                      int64_t ld_out);
+/* Same contraction, enqueued on the compute stream: returns as soon as D is staged; vj / vk (pinned host memory for
+ * real asynchrony) are complete after qemb_ctx_synchronize.  The all-fragment consumer pipeline (mbe.py:1146-1170 done
+ * where (ij|kl) lives) issues it right behind every resident transform, so only nmo x nmo matrices leave the device. */
+int qemb_fragment_jk_enqueue(qemb_workspace *, const double *D_host, int64_t ldd, double *vj_host, double *vk_host,
+                             int64_t ld_out);
 /* device time (ms) of the last qemb_fragment_jk and its algorithmic bytes (8 npair^2) */
 int qemb_fragment_jk_time(const qemb_workspace *, float *ms, double *bytes);
 /* blocks until the host output of the transform that returned `ticket` is complete */
 int qemb_fragment_wait_output(qemb_workspace *, int64_t ticket);
+/* how many host-output transforms may be pending per workspace before the oldest ticket's completion state is
+ * recycled (a caller keeps at most this many output buffers in flight) */
+int qemb_output_ring_depth(void);
 
 /* Algorithmic work of the last planned fragment (SURVEY 8d formulas): flops and bytes of K1, K2a,
  * K2b, K3 in that order (8 doubles). */
@@ -221,6 +241,13 @@ int qemb_ctx_set_k3_int8_slices(qemb_ctx *ctx, int slices);
  * (expo[c]; a column holding NaN / Inf gets the poison value -2^30 and zero digits) and the digits
  * D[(c * slices + a) * nrows + p].  Test hook for the CPU suite; no reference counterpart, not on the product path. */
 int qemb_k3_int8_slice_host(const double *X, int64_t ldx, int64_t nrows, int64_t ncols, int slices, int8_t *D, int *expo);
+/* host DRAM bandwidth seen by the library's host threads: non-temporal fill of `bytes` (write_gbs) and parallel memcpy
+ * of bytes/2 (copy_gbs = bytes copied per second); best of 3.  Denominator of bench.py's e2e.host_roofline_frac. */
+int qemb_host_bandwidth(int64_t bytes, double *write_gbs, double *copy_gbs);
+/* orders an external CUDA stream (cudaStream_t passed as void*, e.g. torch's current stream that NCCL collectives run
+ * on) against the context's compute stream without a host synchronisation: direction 0 = the external stream waits
+ * for everything enqueued on the compute stream so far, 1 = the compute stream waits for the external stream */
+int qemb_ctx_stream_handoff(qemb_ctx *, void *external_stream, int direction);
 /* number of host worker threads of the library (QEMB_HOST_THREADS, default: cores in the affinity mask - 1) */
 int qemb_host_threads(int *n);
 /* G[c + ld*r] = G[r + ld*c] for all r > c of an n x n host matrix (the host half of output mode 1; also the

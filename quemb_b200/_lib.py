@@ -59,6 +59,13 @@ _SIGS = {
     # name: (restype, argtypes)
     "qemb_last_error": (ctypes.c_char_p, []),
     "qemb_version": (ctypes.c_char_p, []),
+    "qemb_get_log_level": (c_int, []),
+    "qemb_set_log_level": (c_int, [c_int]),
+    "qemb_tensor_count_nan": (c_int, [c_p, ctypes.POINTER(c_i64)]),
+    "qemb_fragment_jk_enqueue": (c_int, [c_p, c_p, c_i64, c_p, c_p, c_i64]),
+    "qemb_output_ring_depth": (c_int, []),
+    "qemb_host_bandwidth": (c_int, [c_i64, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
+    "qemb_ctx_stream_handoff": (c_int, [c_p, c_p, c_int]),
     "qemb_device_count": (c_int, [ctypes.POINTER(c_int)]),
     "qemb_ctx_create": (c_int, [c_int, ctypes.POINTER(c_p)]),
     "qemb_ctx_destroy": (None, [c_p]),

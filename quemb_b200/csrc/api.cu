@@ -10,6 +10,8 @@
 // to travel to the host, so that back-to-back qemb_fragment_transform calls pipeline without any
 // host-side wait on the compute stream.
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -27,7 +29,29 @@
 #include "host_pool.h"
 #include "kernels.cuh"
 
+#include <nvtx3/nvToolsExt.h> // header-only NVTX v3: ranges show up under nsys / ncu --nvtx, no-ops otherwise
+
 using namespace qemb;
+
+// ------------------------------------------------------------------------------------------------
+// log level (hpp:24-46: Python logging levels, process global) and NVTX ranges per step
+// ------------------------------------------------------------------------------------------------
+static std::atomic<int> g_log_level{40}; // LogLevel::Error, the reference's default (hpp:34)
+
+extern "C" int qemb_get_log_level(void) { return g_log_level.load(std::memory_order_relaxed); }
+extern "C" int qemb_set_log_level(int level)
+{
+    g_log_level.store(level, std::memory_order_relaxed);
+    return QEMB_OK;
+}
+static inline bool log_info() { return g_log_level.load(std::memory_order_relaxed) <= 20; }
+
+namespace {
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+} // namespace
 
 // ------------------------------------------------------------------------------------------------
 // errors
@@ -226,6 +250,13 @@ struct qemb_tensor {
     std::vector<int64_t> uptr, uidx;       // exch_reachable_unique (hpp:149-162)
     DevBuf data, d_rcol, d_ridx;           // FP64 ldp x n_unique ; int32 copies of rcol / ridx
     DevBuf scratch;                        // column chunk being whitened (qemb_tensor_upload_whitened_rows)
+    // (mu nu|P) block staging (qemb_tensor_scatter_block): two pinned host slots + two device slots, so that
+    // the caller evaluates libcint block b+1 while block b is copied and scattered
+    HostBuf stage_h[2];
+    DevBuf stage_d[2];
+    cudaEvent_t stage_done[2] = {nullptr, nullptr};
+    int stage_k = 0;
+    DevBuf nan_count;
     bool whitened = false;
 };
 
@@ -275,6 +306,7 @@ struct OutJob {
     std::condition_variable cv;
     int64_t remaining = 0; // outstanding mirror tasks + 1 while copy groups are still in flight
     bool active = false;   // this ticket travels as a triangle (wait on the job, not only on the event)
+    bool counted = false;  // ctx->out_pending holds one count for this job (dropped exactly once)
     qemb_ctx *ctx = nullptr;
 };
 
@@ -282,7 +314,8 @@ struct OutJob {
 inline void job_finished(OutJob &job)
 {
     job.cv.notify_all();
-    if (job.ctx) {
+    if (job.ctx && job.counted) {
+        job.counted = false;
         std::lock_guard<std::mutex> lk(job.ctx->out_mutex);
         if (--job.ctx->out_pending == 0) job.ctx->out_cv.notify_all();
     }
@@ -326,6 +359,9 @@ struct qemb_workspace {
     DevBuf gram_i8; // scratch of the opt-in int8-slice K3
     cudaEvent_t jk_ev[2] = {nullptr, nullptr};
     float jk_ms = 0.f;
+    HostBuf jk_stage[2];
+    cudaEvent_t jk_stage_free[2] = {nullptr, nullptr};
+    int jk_stage_k = 0;
     // gram tile lists by number of row tiles
     std::map<int, std::pair<DevBuf, int>> gram_tiles;
     // timing
@@ -538,6 +574,49 @@ extern "C" int qemb_host_free(void *p)
     return QEMB_OK;
 }
 
+// Host DRAM bandwidth as the library's own host threads see it: non-temporal fill of `bytes` (write) and a
+// parallel memcpy of bytes/2 -> bytes/2 (copy: read + write), best of 3.  The denominator of e2e.host_roofline_frac
+// in bench.py: every (ij|kl) matrix has to be WRITTEN into host DRAM once, by the copy engines or by the mirror pass.
+extern "C" int qemb_host_bandwidth(int64_t bytes, double *write_gbs, double *copy_gbs)
+{
+    REQ(bytes >= (1 << 20) && write_gbs && copy_gbs, "bad argument");
+    void *buf = nullptr;
+    if (posix_memalign(&buf, 4096, (size_t)bytes) != 0 || !buf) return fail(QEMB_ENOMEM, "host allocation failed");
+    char *b = static_cast<char *>(buf);
+    parallel_for(bytes, 4 << 20, [=](int64_t i0, int64_t i1) { std::memset(b + i0, 1, (size_t)(i1 - i0)); }); // touch
+    double wbest = 0, cbest = 0;
+    for (int rep = 0; rep < 3; ++rep) {
+        auto t0 = std::chrono::steady_clock::now();
+        parallel_for(bytes, 4 << 20, [=](int64_t i0, int64_t i1) { stream_fill(b + i0, (size_t)(i1 - i0)); });
+        auto t1 = std::chrono::steady_clock::now();
+        parallel_memcpy(b + bytes / 2, b, (size_t)(bytes / 2));
+        auto t2 = std::chrono::steady_clock::now();
+        wbest = std::max(wbest, (double)bytes / std::chrono::duration<double>(t1 - t0).count() / 1e9);
+        cbest = std::max(cbest, (double)(bytes / 2) / std::chrono::duration<double>(t2 - t1).count() / 1e9);
+    }
+    std::free(buf);
+    *write_gbs = wbest;
+    *copy_gbs = cbest;
+    return QEMB_OK;
+}
+
+// Orders an EXTERNAL stream (e.g. torch's current stream, which NCCL collectives are enqueued on) against the
+// library's compute stream without a host synchronisation.  direction 0: work enqueued on `external_stream` after
+// this call waits for everything enqueued on the compute stream so far; direction 1: the reverse.
+extern "C" int qemb_ctx_stream_handoff(qemb_ctx *c, void *external_stream, int direction)
+{
+    REQ(c && (direction == 0 || direction == 1), "bad argument");
+    DeviceGuard g(c->device);
+    cudaStream_t ext = static_cast<cudaStream_t>(external_stream);
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    cudaError_t rc = cudaEventRecord(e, direction == 0 ? c->compute : ext);
+    if (rc == cudaSuccess) rc = cudaStreamWaitEvent(direction == 0 ? ext : c->compute, e, 0);
+    cudaEventDestroy(e); // released once the wait has been satisfied
+    CU(rc);
+    return QEMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // index maps
 // ------------------------------------------------------------------------------------------------
@@ -671,6 +750,12 @@ extern "C" void qemb_tensor_destroy(qemb_tensor *t)
     t->d_rcol.release();
     t->d_ridx.release();
     t->scratch.release();
+    t->nan_count.release();
+    for (int i = 0; i < 2; ++i) {
+        t->stage_h[i].release();
+        t->stage_d[i].release();
+        if (t->stage_done[i]) cudaEventDestroy(t->stage_done[i]);
+    }
     delete t;
 }
 
@@ -713,7 +798,12 @@ extern "C" int qemb_tensor_upload(qemb_tensor *t, const double *host, int64_t ld
     REQ(col0 >= 0 && ncols >= 0 && col0 + ncols <= t->n_unique, "column range outside the tensor");
     REQ(ld_host >= t->naux, "ld_host < naux");
     if (ncols == 0) return QEMB_OK;
+    // a partial refresh of a whitened tensor would leave raw and L^-1-scaled columns side by side under one flag:
+    // replace everything, or clear the flag first (qemb_tensor_set_whitened(t, 0)) and whiten again afterwards
+    REQ(!t->whitened || (col0 == 0 && ncols == t->n_unique),
+        "partial upload into a whitened tensor (call qemb_tensor_set_whitened(t, 0) first)");
     DeviceGuard g(t->ctx->device);
+    NvtxRange nv("qemb:tensor_upload");
     cudaStream_t s = t->ctx->compute;
     TRY(upload_2d(t->ctx, t->data.as<double>() + col0 * t->ldp, (size_t)t->ldp * 8, host, (size_t)ld_host * 8,
                   (size_t)t->naux * 8, (size_t)ncols, s));
@@ -746,19 +836,51 @@ extern "C" int qemb_tensor_scatter_block(qemb_tensor *t, const double *block, in
             }
         }
     if (live == 0) return QEMB_OK;
+    REQ(!t->whitened, "block staging into a whitened tensor (call qemb_tensor_set_whitened(t, 0) first)");
     DeviceGuard g(t->ctx->device);
+    NvtxRange nv("qemb:scatter_block");
     cudaStream_t s = t->ctx->compute;
     const size_t bbytes = (size_t)npairs * (size_t)t->naux * 8, cbytes = (size_t)npairs * 4;
     const size_t coff = (bbytes + 15) & ~size_t(15);
-    TRY(t->scratch.reserve(coff + cbytes));
-    char *d = static_cast<char *>(t->scratch.p);
-    TRY(upload_2d(t->ctx, d, bbytes, block, bbytes, bbytes, 1, s));
-    CU(cudaMemcpyAsync(d + coff, col.data(), cbytes, cudaMemcpyHostToDevice, s));
+    // two staging slots: the host copy of this block into pinned memory overlaps the H2D copy + scatter kernel of the
+    // previous one, and the call returns as soon as the block is in the slot (the caller's buffer is free again)
+    const int k = t->stage_k;
+    t->stage_k ^= 1;
+    if (!t->stage_done[k]) CU(cudaEventCreateWithFlags(&t->stage_done[k], cudaEventDisableTiming));
+    CU(cudaEventSynchronize(t->stage_done[k])); // never recorded = complete
+    TRY(t->stage_h[k].reserve(coff + cbytes));
+    TRY(t->stage_d[k].reserve(coff + cbytes));
+    char *h = static_cast<char *>(t->stage_h[k].p);
+    if (bbytes >= (8u << 20))
+        parallel_memcpy(h, block, bbytes);
+    else
+        std::memcpy(h, block, bbytes);
+    std::memcpy(h + coff, col.data(), cbytes);
+    char *d = static_cast<char *>(t->stage_d[k].p);
+    CU(cudaMemcpyAsync(d, h, coff + cbytes, cudaMemcpyHostToDevice, s));
+    t->ctx->h2d_bytes += (int64_t)(coff + cbytes);
     CU(launch_scatter_block(reinterpret_cast<const double *>(d), reinterpret_cast<const int *>(d + coff), (int)npairs,
                             (int)t->naux, t->data.as<double>(), t->ldp, s));
     t->ctx->launches += 1;
-    CU(cudaStreamSynchronize(s)); // col (host vector) and the caller's block may be reused
-    t->whitened = false;
+    CU(cudaEventRecord(t->stage_done[k], s));
+    return QEMB_OK;
+}
+
+// NaN entries left in the tensor (a column nobody filled keeps the NaN of qemb_tensor_create): the reference asserts
+// `not np.isnan(result.unique_dense_data).any()` after staging (py:492)
+extern "C" int qemb_tensor_count_nan(qemb_tensor *t, int64_t *n)
+{
+    REQ(t && n, "null argument");
+    DeviceGuard g(t->ctx->device);
+    cudaStream_t s = t->ctx->compute;
+    TRY(t->nan_count.reserve(8));
+    CU(cudaMemsetAsync(t->nan_count.p, 0, 8, s));
+    CU(launch_count_nan(t->data.as<double>(), t->ldp, t->naux, t->n_unique, t->nan_count.as<unsigned long long>(), s));
+    t->ctx->launches += 1;
+    unsigned long long v = 0;
+    CU(cudaMemcpyAsync(&v, t->nan_count.p, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    *n = (int64_t)v;
     return QEMB_OK;
 }
 
@@ -1043,6 +1165,10 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     for (auto &e : w->jk_ev)
         if (e) cudaEventDestroy(e);
     w->gram_i8.release();
+    for (int i = 0; i < 2; ++i) {
+        w->jk_stage[i].release();
+        if (w->jk_stage_free[i]) cudaEventDestroy(w->jk_stage_free[i]);
+    }
     w->jk_in.release();
     w->gram_partial.release();
     w->jk_scratch.release();
@@ -1716,6 +1842,7 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         std::lock_guard<std::mutex> lk(job.m);
         job.remaining = 1;
         job.active = true;
+        job.counted = true;
         job.ctx = w->ctx;
         std::lock_guard<std::mutex> lk2(w->ctx->out_mutex);
         w->ctx->out_pending += 1;
@@ -1733,15 +1860,21 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         if (!whole && c1 > csplit) c1 = csplit; // groups do not straddle the split
         if (n - c1 < 256 && (whole || csplit == n)) c1 = n;
         w->ctx->d2h_bytes += rows * 8 * (c1 - c0);
-        CU(cudaMemcpy2DAsync(out + r_first + ld_out * c0, (size_t)ld_out * 8, G + r_first + n * c0, (size_t)n * 8,
-                             (size_t)rows * 8, (size_t)(c1 - c0), cudaMemcpyDeviceToHost, cs));
-        MirrorCb *cb = new MirrorCb{&job, out, ld_out, n, c0, c1, c1 == n, whole ? c1 : csplit};
-        cudaError_t e = cudaLaunchHostFunc(cs, mirror_callback, cb);
+        cudaError_t e = cudaMemcpy2DAsync(out + r_first + ld_out * c0, (size_t)ld_out * 8, G + r_first + n * c0, (size_t)n * 8,
+                                          (size_t)rows * 8, (size_t)(c1 - c0), cudaMemcpyDeviceToHost, cs);
+        MirrorCb *cb = nullptr;
+        if (e == cudaSuccess) {
+            cb = new MirrorCb{&job, out, ld_out, n, c0, c1, c1 == n, whole ? c1 : csplit};
+            e = cudaLaunchHostFunc(cs, mirror_callback, cb);
+        }
         if (e != cudaSuccess) {
+            // no further callback will drop the sentinel: drop it here so that wait_job / qemb_workspace_destroy do
+            // not block forever (callbacks already queued only add and remove their own mirror tasks)
             delete cb;
-            std::lock_guard<std::mutex> lk(job.m);
-            job.remaining = 0; // nothing will ever signal this job
-            job_finished(job);
+            {
+                std::lock_guard<std::mutex> lk(job.m);
+                if (--job.remaining == 0) job_finished(job);
+            }
             CU(e);
         }
         c0 = c1;
@@ -1751,10 +1884,9 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
 
 } // namespace
 
-extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, const qemb_metric *m,
-                                       const qemb_screen *sc, const double *TA, int64_t ld, int64_t nao, int64_t nmo,
-                                       double eps, int64_t p_begin, int64_t p_end, double *out, int64_t ld_out,
-                                       int out_is_device, int64_t *ticket)
+static int transform_impl(qemb_workspace *w, const qemb_tensor *t, const qemb_metric *m, const qemb_screen *sc,
+                          const double *TA, int64_t ld, int64_t nao, int64_t nmo, double eps, int64_t p_begin,
+                          int64_t p_end, double *out, int64_t ld_out, int out_is_device, int64_t *ticket)
 {
     if (ticket) *ticket = -1;
     REQ(w && t && sc && TA, "null argument");
@@ -1762,10 +1894,23 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
     REQ(!out || ld_out >= nmo * (nmo + 1) / 2, "ld_out < npair");
     DeviceGuard g(w->ctx->device);
     reset_events(w);
-    TRY(qemb_fragment_screen(w, sc, TA, ld, nao, nmo, eps, nullptr));
-    TRY(contract_1st(w, t, p_begin, p_end));
-    TRY(contract_2nd(w));
-    if (!t->whitened) TRY(solve(w, m));
+    {
+        NvtxRange nv("qemb:screen");
+        TRY(qemb_fragment_screen(w, sc, TA, ld, nao, nmo, eps, nullptr));
+    }
+    {
+        NvtxRange nv("qemb:K1");
+        TRY(contract_1st(w, t, p_begin, p_end));
+    }
+    {
+        NvtxRange nv("qemb:K2a");
+        TRY(contract_2nd(w));
+    }
+    if (!t->whitened) {
+        NvtxRange nv("qemb:K2b");
+        TRY(solve(w, m));
+    }
+    NvtxRange nv3("qemb:K3+output");
     Slot &s = w->slot[w->cur];
     if (out && out_is_device) return gram(w, out, ld_out, out_is_device == 2);
     TRY(gram_ws(w));
@@ -1789,8 +1934,36 @@ extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, 
     return QEMB_OK;
 }
 
+extern "C" int qemb_fragment_transform(qemb_workspace *w, const qemb_tensor *t, const qemb_metric *m,
+                                       const qemb_screen *sc, const double *TA, int64_t ld, int64_t nao, int64_t nmo,
+                                       double eps, int64_t p_begin, int64_t p_end, double *out, int64_t ld_out,
+                                       int out_is_device, int64_t *ticket)
+{
+    REQ(w, "null workspace");
+    NvtxRange nv("qemb:fragment_transform");
+    // log level <= Info (hpp:170-204, the reference's Timer prints "[TIMER] <function> finished in <t> s" per step):
+    // per-kernel CUDA-event times of this fragment.  Reading them waits for the fragment, i.e. Info-level logging
+    // serialises the fragment pipeline -- like the reference's std::cout lines it is a diagnostic mode.
+    const bool info = log_info();
+    const bool saved = w->ctx->timing;
+    if (info) w->ctx->timing = true;
+    const int rc = transform_impl(w, t, m, sc, TA, ld, nao, nmo, eps, p_begin, p_end, out, ld_out, out_is_device, ticket);
+    w->ctx->timing = saved;
+    if (info && rc == QEMB_OK) {
+        float ms[5];
+        if (qemb_fragment_times(w, ms) == QEMB_OK) {
+            static const char *names[5] = {"get_AO_per_MO", "contract_with_TA_1st", "contract_with_TA_2nd_to_sym_dense",
+                                           "eval_via_cholesky:trsm", "eval_via_cholesky:gram"};
+            for (int i = 0; i < 5; ++i)
+                if (i != 3 || ms[3] > 0.f) std::printf("[TIMER] %s finished in %g s\n", names[i], (double)ms[i] * 1e-3);
+            std::fflush(stdout);
+        }
+    }
+    return rc;
+}
+
 // J/K of a symmetric density from the (ij|kl) the last transform left on the device (jk.cu).
-extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd, double *vj, double *vk, int64_t ldo)
+static int jk_impl(qemb_workspace *w, const double *D, int64_t ldd, double *vj, double *vk, int64_t ldo, bool sync)
 {
     REQ(w && D && vj && vk && w->have_G, "null argument or no (ij|kl) on the device");
     const Slot &s = w->slot[w->cur];
@@ -1805,6 +1978,7 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
         }
     REQ(amax <= 1e-12 * std::max(dmax, 1e-300) || amax == 0.0, "density matrix must be symmetric (hermi=1)");
     DeviceGuard g(w->ctx->device);
+    NvtxRange nv("qemb:jk");
     cudaStream_t cs = w->ctx->compute;
     // chunk table: whole packed rows, at most jk_chunk_doubles() doubles per chunk
     std::vector<int> crow{0};
@@ -1833,18 +2007,26 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     // (dpk 16-byte aligned and padded by two doubles: jk_stream.cu copies whole rows of it with 16-byte bulk copies)
     const size_t oD = 0, oP = ((size_t)nmo * nmo * 8 + 15) / 16 * 16, oC = oP + ((size_t)npair + 2) * 8;
     const size_t in_bytes = oC + crow.size() * 4;
-    std::vector<double> hin((in_bytes + 7) / 8);
+    // host staging in pinned memory, two slots: an enqueued (asynchronous) call returns while its copy is in flight
+    const int hk = w->jk_stage_k;
+    w->jk_stage_k ^= 1;
+    if (!w->jk_stage_free[hk]) CU(cudaEventCreateWithFlags(&w->jk_stage_free[hk], cudaEventDisableTiming));
+    CU(cudaEventSynchronize(w->jk_stage_free[hk]));
+    TRY(w->jk_stage[hk].reserve(in_bytes + 8));
+    double *hin = static_cast<double *>(w->jk_stage[hk].p);
+    std::memset(hin, 0, in_bytes + 8);
     for (int64_t l = 0; l < nmo; ++l)
         for (int64_t k = 0; k < nmo; ++k) hin[k + nmo * l] = D[k + ldd * l];
     for (int64_t k = 0; k < nmo; ++k)
         for (int64_t l = 0; l <= k; ++l) hin[oP / 8 + k * (k + 1) / 2 + l] = (k == l ? 1.0 : 2.0) * D[k + ldd * l];
-    std::memcpy(reinterpret_cast<char *>(hin.data()) + oC, crow.data(), crow.size() * 4);
+    std::memcpy(reinterpret_cast<char *>(hin) + oC, crow.data(), crow.size() * 4);
     TRY(w->jk_in.reserve(in_bytes));
     const int njp1 = stream ? 1 : jk_warps();
     const int64_t njp = npair * njp1;
     TRY(w->jk_scratch.reserve(((size_t)njp + 2 * (size_t)npair * nmo) * 8));
     TRY(w->jk_out.reserve(2 * (size_t)nmo * nmo * 8));
-    CU(cudaMemcpyAsync(w->jk_in.p, hin.data(), in_bytes, cudaMemcpyHostToDevice, cs));
+    CU(cudaMemcpyAsync(w->jk_in.p, hin, in_bytes, cudaMemcpyHostToDevice, cs));
+    CU(cudaEventRecord(w->jk_stage_free[hk], cs));
     w->ctx->h2d_bytes += (int64_t)in_bytes;
     JkParams p;
     p.G = w->G_last;
@@ -1876,15 +2058,40 @@ extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd,
     CU(cudaMemcpy2DAsync(vj, (size_t)ldo * 8, Jd, (size_t)nmo * 8, (size_t)nmo * 8, (size_t)nmo, cudaMemcpyDeviceToHost, cs));
     CU(cudaMemcpy2DAsync(vk, (size_t)ldo * 8, Kd, (size_t)nmo * 8, (size_t)nmo * 8, (size_t)nmo, cudaMemcpyDeviceToHost, cs));
     w->ctx->d2h_bytes += 2 * nmo * nmo * 8;
-    CU(cudaStreamSynchronize(cs));
-    CU(cudaEventElapsedTime(&w->jk_ms, w->jk_ev[0], w->jk_ev[1]));
+    w->jk_ms = -1.f;
+    if (sync) {
+        CU(cudaStreamSynchronize(cs));
+        CU(cudaEventElapsedTime(&w->jk_ms, w->jk_ev[0], w->jk_ev[1]));
+    }
     return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_jk(qemb_workspace *w, const double *D, int64_t ldd, double *vj, double *vk, int64_t ldo)
+{
+    return jk_impl(w, D, ldd, vj, vk, ldo, true);
+}
+
+// Same, enqueued: returns once the density has been staged; vj / vk (pinned host memory for true asynchrony) are
+// complete after qemb_ctx_synchronize.  The all-fragment consumer pipeline (driver.build_consumed) calls this right
+// behind every resident transform, so that only nmo x nmo matrices ever leave the device and the compute stream
+// never idles between fragments.
+extern "C" int qemb_fragment_jk_enqueue(qemb_workspace *w, const double *D, int64_t ldd, double *vj, double *vk,
+                                        int64_t ldo)
+{
+    return jk_impl(w, D, ldd, vj, vk, ldo, false);
 }
 
 // device time of the last qemb_fragment_jk (both kernels) and its algorithmic bytes (8 npair^2: G read once)
 extern "C" int qemb_fragment_jk_time(const qemb_workspace *w, float *ms, double *bytes)
 {
     REQ(w && ms, "null argument");
+    if (w->jk_ms < 0.f && w->jk_ev[0] && w->jk_ev[1]) { // last call was enqueued: its events complete in stream order
+        DeviceGuard g(w->ctx->device);
+        CU(cudaEventSynchronize(w->jk_ev[1]));
+        float ms_ = 0.f;
+        CU(cudaEventElapsedTime(&ms_, w->jk_ev[0], w->jk_ev[1]));
+        const_cast<qemb_workspace *>(w)->jk_ms = ms_;
+    }
     *ms = w->jk_ms;
     if (bytes) {
         const double np = (double)w->slot[w->cur].npair;
@@ -1967,6 +2174,10 @@ extern "C" int qemb_device_to_host(qemb_ctx *c, void *host, const void *dev, int
     CU(cudaStreamSynchronize(c->compute));
     return QEMB_OK;
 }
+
+// how many host-output transforms may be in flight per workspace before the oldest ticket's completion state is
+// recycled (callers keep at most this many pinned output buffers pending)
+extern "C" int qemb_output_ring_depth(void) { return OUT_RING - 1; }
 
 extern "C" int qemb_fragment_wait_output(qemb_workspace *w, int64_t ticket)
 {

@@ -204,6 +204,25 @@ void parallel_for(int64_t n, int64_t grain, const std::function<void(int64_t, in
     cv.wait(lk, [&] { return left == 0; });
 }
 
+__attribute__((target("avx2"))) static void stream_fill_avx2(char *c, size_t bytes)
+{
+    size_t i = 0;
+    while (i < bytes && (reinterpret_cast<uintptr_t>(c + i) & 31)) c[i++] = 0;
+    const __m256i z = _mm256_setzero_si256();
+    for (; i + 32 <= bytes; i += 32) _mm256_stream_si256(reinterpret_cast<__m256i *>(c + i), z);
+    for (; i < bytes; ++i) c[i] = 0;
+    _mm_sfence();
+}
+
+void stream_fill(void *p, size_t bytes)
+{
+    static const bool have_avx2 = __builtin_cpu_supports("avx2");
+    if (have_avx2)
+        stream_fill_avx2(static_cast<char *>(p), bytes);
+    else
+        std::memset(p, 0, bytes);
+}
+
 void parallel_memcpy(void *dst, const void *src, size_t bytes)
 {
     const int64_t chunk = 4 << 20;

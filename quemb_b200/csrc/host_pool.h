@@ -38,6 +38,9 @@ void mirror_block(double *G, int64_t ld, int64_t c0, int64_t c1, int64_t r0, int
 // fn(i0, i1) over [0, n) in chunks of `grain` on the pool; blocks until done
 void parallel_for(int64_t n, int64_t grain, const std::function<void(int64_t, int64_t)> &fn);
 
+// fills `bytes` at p with zeros using non-temporal stores where aligned (host write-bandwidth probe)
+void stream_fill(void *p, size_t bytes);
+
 // multi-threaded memcpy (used to stage pageable host data through pinned memory); blocks until done
 void parallel_memcpy(void *dst, const void *src, size_t bytes);
 

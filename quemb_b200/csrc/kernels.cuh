@@ -129,6 +129,9 @@ cudaError_t launch_zero_rows(double *p, int64_t ld, int64_t r0, int64_t r1, int6
 
 cudaError_t launch_scatter_block(const double *block, const int *col, int npairs, int naux, double *M, int64_t ld,
                                  cudaStream_t s);
+// *out += number of NaN entries in rows [0, nrows) of `ncol` columns (out: zeroed device counter)
+cudaError_t launch_count_nan(const double *p, int64_t ld, int64_t nrows, int64_t ncol, unsigned long long *out,
+                             cudaStream_t s);
 cudaError_t launch_set_diag(double *p, int64_t ld, int64_t i0, int64_t i1, double v, cudaStream_t s);
 
 } // namespace qemb

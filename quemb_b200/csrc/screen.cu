@@ -83,6 +83,29 @@ cudaError_t launch_scatter_block(const double *block, const int *col, int npairs
     return cudaGetLastError();
 }
 
+// number of NaN entries in rows [0, nrows) of the columns of a column-major matrix (the reference's
+// `assert not np.isnan(result.unique_dense_data).any()` after staging, eri_sparse_DF.py:492)
+__global__ void count_nan_kernel(const double *__restrict__ p, int64_t ld, int64_t nrows, int64_t ncol,
+                                 unsigned long long *__restrict__ out)
+{
+    const int64_t total = nrows * ncol;
+    unsigned long long n = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t c = i / nrows, r = i - c * nrows;
+        const double v = p[c * ld + r];
+        n += (v != v);
+    }
+    for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(out, n);
+}
+cudaError_t launch_count_nan(const double *p, int64_t ld, int64_t nrows, int64_t ncol, unsigned long long *out,
+                             cudaStream_t s)
+{
+    if (nrows <= 0 || ncol <= 0) return cudaSuccess;
+    count_nan_kernel<<<148 * 8, 256, 0, s>>>(p, ld, nrows, ncol, out);
+    return cudaGetLastError();
+}
+
 __global__ void set_diag_kernel(double *p, int64_t ld, int64_t i0, int64_t i1, double v)
 {
     const int64_t i = i0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;

@@ -11,6 +11,7 @@
 // Panels are independent, so there is no inter-CTA dependency and one launch solves everything.
 // Only diagonal blocks are inverted (like cuBLAS/MAGMA trsm), never the whole factor, which keeps the
 // backward stability of substitution for the ill-conditioned Coulomb metric.
+#include <algorithm>
 #include "dmma_core.cuh"
 #include "kernels.cuh"
 
@@ -188,6 +189,10 @@ cudaError_t launch_trsm_rows(const TrsmParams &p, int mrows, cudaStream_t s)
     if (e != cudaSuccess) return e;
     if (p.ncol <= 0 || p.nblocks <= 0) return cudaSuccess;
     TrsmKParams kp{p, mrows};
+    // forward substitution never needs block rows below the last valid row: a slab that ends at row p_end costs
+    // p_end^2 ncol flops, not naux^2 ncol (aux-sharded staging: rank r solves only down to its own slab)
+    kp.p.nblocks = std::min(p.nblocks, (mrows + NB - 1) / NB);
+    if (kp.p.nblocks <= 0) return cudaSuccess;
     const unsigned grid = (unsigned)((p.ncol + PN - 1) / PN);
     trsm_panel_kernel<<<grid, NTHREADS, SMEM_BYTES, s>>>(kp);
     return cudaGetLastError();

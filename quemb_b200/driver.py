@@ -7,25 +7,36 @@ QuEmb).  Differences, all behind the same seam:
 
 * (P|mu nu), L and S_abs are uploaded once and stay in HBM; per fragment only ``TA`` goes up and G comes
   back (the reference's GPU variant re-uploads (P|ij) and mallocs per fragment, ``cpp:642-660``);
+* (P|mu nu) is staged block by block straight into HBM (``staging.get_sparse_P_mu_nu``), never through a host
+  copy and never through the reference's per-pair Python scatter (``eri_sparse_DF.py:476-488``);
 * the metric is applied once to (P|mu nu) (``whiten=True``, design option O1) instead of once per
   fragment;
 * calls are pipelined: while the sink consumes fragment f-1 and the copy engine drains G(f), the
-  compute stream already works on fragment f+1;
+  compute stream already works on fragment f+1; a sink may return a ``Future`` (the background dataset writer
+  does) and the pinned buffer it was handed is only reused once that future is done;
 * fragments are partitioned over ranks (one process per GPU, ``torch.distributed``) or over several
-  devices of one process (one thread per device, dynamic queue) with no data-path collective.
+  devices of one process (one thread per device, dynamic queue) with no data-path collective;
+* a consumer that only needs J/K-type contractions of every fragment's (ij|kl) (``BE.initialize``,
+  ``mbe.py:1146-1170``) runs where the matrix lives (:meth:`FragmentERIBuilder.build_jk`): only ``nmo x nmo``
+  matrices leave the device.
 """
 
 from __future__ import annotations
 
+import logging
 import threading
+from concurrent.futures import Future
 from typing import Callable, Sequence
 
 import numpy as np
 
 from . import _lib
 from . import eri_sparse_DF as q
+from . import staging
 
-Sink = Callable[[int, np.ndarray], None]
+logger = logging.getLogger(__name__)
+
+Sink = Callable[[int, np.ndarray], "Future | None"]
 
 
 def fragment_cost(naux: int, nmo: int, nao: int | None = None) -> float:
@@ -56,7 +67,15 @@ class FragmentERIBuilder:
         self.metric: q.GPU_MatrixHandle | None = None
         self.screen = None
         self._bufs: list[np.ndarray] = []
-        self._n_host_buffers = n_host_buffers
+        # the library keeps completion state for `output_ring_depth()` pending host outputs per workspace; more
+        # buffers than that would let a ticket be recycled before anybody waited for it
+        depth = q.output_ring_depth()
+        if n_host_buffers < 1:
+            raise ValueError("n_host_buffers must be >= 1")
+        if n_host_buffers > depth:
+            logger.warning("n_host_buffers=%d clamped to the library's output ring depth %d", n_host_buffers, depth)
+        self._n_host_buffers = min(n_host_buffers, depth)
+        self.borderline_total = 0
         if max_nmo:
             self.reserve_host(max_nmo)
 
@@ -70,6 +89,23 @@ class FragmentERIBuilder:
         self.screen = q._ScreenHandle(np.asarray(S_abs), self.ctx) if not isinstance(S_abs, q._ScreenHandle) else S_abs
         if whiten and not self.tensor.whitened:
             self.tensor.whiten(self.metric)
+
+    def stage_distributed(self, unique_dense_data: np.ndarray, L_PQ, S_abs, dist, *, tensor: q.SemiSparseSym3DTensor,
+                          group=None) -> None:
+        """Fragment-parallel ranks, every one holding the host array: rank r uploads only ITS 1/world share of the
+        columns of (P|mu nu), whitens that share, and the shares are exchanged on the device with NCCL broadcasts
+        over NVLink (``SemiSparseSym3DTensor.whiten_distributed``) -- one host->device pass of the tensor per NODE
+        instead of one per rank, and 1/world of the metric solve each."""
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        n = tensor._n_unique
+        c0, c1 = (n * rank) // world, (n * (rank + 1)) // world
+        self.tensor = tensor
+        self.metric = q.GPU_MatrixHandle(L_PQ, ctx=self.ctx) if not isinstance(L_PQ, q.GPU_MatrixHandle) else L_PQ
+        self.screen = q._ScreenHandle(np.asarray(S_abs), self.ctx) if not isinstance(S_abs, q._ScreenHandle) else S_abs
+        tensor.set_whitened(False)
+        if c1 > c0:
+            tensor.upload(unique_dense_data[:, c0:c1], col0=c0)
+        tensor.whiten_distributed(self.metric, dist, group=group)
 
     def reserve_host(self, max_nmo: int) -> None:
         npair = max_nmo * (max_nmo + 1) // 2
@@ -90,7 +126,9 @@ class FragmentERIBuilder:
     def build(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, sink: Sink | None = None,
               indices: Sequence[int] | None = None) -> None:
         """Transform the fragments ``indices`` (default: all) and hand every G to ``sink(i, G)``.
-        ``G`` is a view of a pinned staging buffer, valid only during the sink call."""
+        ``G`` is a view of a pinned staging buffer, valid during the sink call -- or, when the sink returns a
+        ``concurrent.futures.Future`` (e.g. :class:`quemb_b200.eri_file.AsyncDatasetWriter`), until that future
+        is done: the buffer is not handed to the device again before."""
         assert self.tensor is not None, "stage() first"
         idx = list(range(len(TAs))) if indices is None else list(indices)
         if not idx:
@@ -98,28 +136,48 @@ class FragmentERIBuilder:
         self.reserve_host(max(TAs[i].shape[1] for i in idx))
         nb = len(self._bufs)
         metric = None if self.tensor.whitened else self.metric
-        pending: list[tuple[int, int, np.ndarray]] = []  # (fragment, ticket, view)
+        pending: list[tuple[int, int, np.ndarray, int]] = []  # (fragment, ticket, view, buffer)
+        busy: list[Future | None] = [None] * nb  # sink still reading buffer k
 
         def drain_one():
-            i, ticket, view = pending.pop(0)
+            i, ticket, view, kb = pending.pop(0)
             self.ws.wait_output(ticket)
             if sink is not None:
-                sink(i, view)
+                fut = sink(i, view)
+                busy[kb] = fut if isinstance(fut, Future) else None
 
         for k, i in enumerate(idx):
             TA = TAs[i]
             nmo = TA.shape[1]
             npair = nmo * (nmo + 1) // 2
+            kb = k % nb
             if len(pending) >= nb:  # the buffer about to be reused must have been consumed
                 drain_one()
-            view = self._bufs[k % nb][: npair * npair].reshape(npair, npair)
+            if busy[kb] is not None:
+                busy[kb].result()
+                busy[kb] = None
+            view = self._bufs[kb][: npair * npair].reshape(npair, npair)
             q.transform_integral(self.tensor, TA, self.screen, metric, MO_coeff_epsilon, ws=self.ws, out=view,
                                  synchronize=False)
-            pending.append((i, self.ws.last_ticket, view))
+            self._note_borderline(i)
+            pending.append((i, self.ws.last_ticket, view, kb))
             if len(pending) >= nb:
                 drain_one()
         while pending:
             drain_one()
+        for f in busy:
+            if f is not None:
+                f.result()
+
+    def _note_borderline(self, i: int) -> None:
+        """Screening entries within 1e-12 of the threshold may fall on the other side in an implementation that sums
+        in another order (the reference's Eigen GEMM is blocked, FMA and -ffast-math): say so instead of silently
+        producing lists that can differ from the reference's."""
+        n = self.ws.borderline
+        if n:
+            self.borderline_total += n
+            logger.warning("fragment %d: %d screening entries within 1e-12 of MO_coeff_epsilon; A(i) may differ from "
+                           "an implementation that sums S_abs*TA in another order", i, n)
 
     def build_device(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, out_dev_ptr: int, ld_out: int | None = None,
                      indices: Sequence[int] | None = None) -> None:
@@ -134,19 +192,59 @@ class FragmentERIBuilder:
             q.transform_integral_device(self.tensor, TAs[i], self.screen, metric, MO_coeff_epsilon, out_dev_ptr,
                                         ld_out or npair, ws=self.ws)
 
+    def build_jk(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float,
+                 densities: Callable[[int], Sequence[np.ndarray]], indices: Sequence[int] | None = None,
+                 ) -> dict[int, list[tuple[np.ndarray, np.ndarray]]]:
+        """The all-fragment CONSUMER pipeline: every fragment is transformed with (ij|kl) left
+        resident, ``scf.hf.dot_eri_dm``-type J/K contractions with the symmetric ``(nmo, nmo)`` matrices
+        ``densities(i)`` are enqueued right behind it on the same stream, and only the ``nmo x nmo`` results travel
+        to the host (pinned, asynchronous).  Nothing of size ``npair^2`` ever leaves HBM, so the host-memory bound of
+        the full delivery does not apply.  Returns ``{i: [(vj, vk), ...]}``."""
+        assert self.tensor is not None, "stage() first"
+        idx = list(range(len(TAs))) if indices is None else list(indices)
+        metric = None if self.tensor.whitened else self.metric
+        dms = {i: [np.asfortranarray(d, dtype=np.float64) for d in densities(i)] for i in idx}
+        total = sum(2 * len(dms[i]) * TAs[i].shape[1] ** 2 for i in idx)
+        pool = _lib.pinned_empty((max(total, 1),))
+        out: dict[int, list[tuple[np.ndarray, np.ndarray]]] = {}
+        views: dict[int, list[tuple[np.ndarray, np.ndarray]]] = {}
+        off = 0
+        try:
+            for i in idx:
+                nmo = TAs[i].shape[1]
+                q.transform_integral_resident(self.tensor, TAs[i], self.screen, metric, MO_coeff_epsilon, ws=self.ws)
+                self._note_borderline(i)
+                views[i] = []
+                for d in dms[i]:
+                    vj = pool[off: off + nmo * nmo].reshape(nmo, nmo, order="F")
+                    vk = pool[off + nmo * nmo: off + 2 * nmo * nmo].reshape(nmo, nmo, order="F")
+                    off += 2 * nmo * nmo
+                    self.ws.jk_enqueue(d, vj, vk)
+                    views[i].append((vj, vk))
+            self.ctx.synchronize()
+            for i in idx:
+                out[i] = [(np.array(vj), np.array(vk)) for vj, vk in views[i]]
+        finally:
+            self.ctx.synchronize()
+            _lib.pinned_free(pool)
+        return out
+
 
 def build_all_fragments(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, TAs, MO_coeff_epsilon, sink: Sink,
-                        *, devices: Sequence[int] = (0,), whiten: bool = True) -> None:
-    """One process, one thread per device, fragments handed out dynamically (largest first)."""
+                        *, devices: Sequence[int] = (0,), whiten: bool = True,
+                        tensors: Sequence[q.SemiSparseSym3DTensor] | None = None) -> None:
+    """One process, one thread per device, fragments handed out dynamically (largest first).  ``tensors`` (one per
+    device, already staged) replaces ``unique_dense_data``."""
     naux = shape[0]
     order = sorted(range(len(TAs)), key=lambda i: -fragment_cost(naux, TAs[i].shape[1]))
     lock = threading.Lock()
     errors: list[BaseException] = []
 
-    def worker(dev: int):
+    def worker(k: int, dev: int):
         try:
             b = FragmentERIBuilder(dev)
-            b.stage(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, whiten=whiten)
+            b.stage(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, whiten=whiten,
+                    tensor=None if tensors is None else tensors[k])
             while True:
                 with lock:
                     if not order:
@@ -157,7 +255,7 @@ def build_all_fragments(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, T
         except BaseException as e:  # noqa: BLE001
             errors.append(e)
 
-    threads = [threading.Thread(target=worker, args=(d,)) for d in devices]
+    threads = [threading.Thread(target=worker, args=(k, d)) for k, d in enumerate(devices)]
     for t in threads:
         t.start()
     for t in threads:
@@ -167,58 +265,68 @@ def build_all_fragments(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, T
 
 
 # ---------------------------------------------------------------------------
-# QuEmb seam (needs quemb + pyscf + h5py in the environment)
+# QuEmb seam (needs quemb + pyscf in the environment)
 # ---------------------------------------------------------------------------
 
 
 def transform_sparse_DF_integral_b200(mf, Fobjs, auxbasis, file_eri_handler, AO_coeff_epsilon: float,
                                       MO_coeff_epsilon: float, n_threads: int = 1, precompute_P_mu_nu: bool = True,
-                                      devices: Sequence[int] = (0,)) -> None:
+                                      devices: Sequence[int] = (0,), async_write: bool = True) -> None:
     """Drop-in sibling of ``transform_sparse_DF_integral_gpu`` (``eri_sparse_DF.py:683-704``).
 
-    Host-side one-offs stay exactly the reference's own functions (``approx_S_abs``, libcint
-    ``int2c2e`` / ``int3c2e`` through ``get_sparse_P_mu_nu``, SciPy Cholesky); everything after them
-    runs on the B200.  Writes dataset ``fobj.dname`` of shape ``(npair, npair)`` float64 per fragment
-    (``eri_sparse_DF.py:630-631``)."""
+    Host-side one-offs that need libcint stay the reference's own functions (``approx_S_abs``, ``int2c2e``,
+    ``_aux_e2`` = ``int3c2e`` blocks, SciPy Cholesky); the AO-AO screening rule and the block loop of
+    ``get_sparse_P_mu_nu`` are restated in :mod:`quemb_b200.staging` and land the integrals directly in HBM.
+    Writes dataset ``fobj.dname`` of shape ``(npair, npair)`` float64 per fragment (``eri_sparse_DF.py:630-631``);
+    with ``async_write`` the ``create_dataset`` calls run on a background thread fed from the pinned output ring.
+    ``n_threads`` is accepted for signature compatibility: fragments are pipelined on the device instead."""
     from pyscf.ao2mo.addons import restore  # noqa: PLC0415
     from pyscf.df.addons import make_auxmol  # noqa: PLC0415
     from quemb.molbe import eri_sparse_DF as ref  # noqa: PLC0415
     from scipy.linalg import cholesky  # noqa: PLC0415
+
+    from .eri_file import AsyncDatasetWriter  # noqa: PLC0415
+
+    q.set_log_level(logging.getLogger().getEffectiveLevel())  # eri_sparse_DF.py:605
 
     mol = mf.mol
     auxmol = make_auxmol(mol, auxbasis=auxbasis)
     S_abs = ref.approx_S_abs(mol)
     PQ = auxmol.intor("int2c2e")
     L = cholesky(PQ, lower=True)
+    nao, naux = int(mol.nao), int(auxmol.nao)
+    TAs = [np.asfortranarray(f.TA) for f in Fobjs]
 
-    def sink_for(fobjs):
-        def sink(i: int, G: np.ndarray) -> None:
-            eri = restore("4", G, fobjs[i].TA.shape[1])
-            file_eri_handler.create_dataset(fobjs[i].dname, data=eri)
-        return sink
-
+    writer = AsyncDatasetWriter(file_eri_handler) if async_write else None
     lock = threading.Lock()
 
-    def locked(sink):
-        def s(i, G):
-            with lock:  # h5py serialises writers anyway
-                sink(i, G)
-        return s
+    def sink(i: int, G: np.ndarray):
+        eri = restore("4", G, Fobjs[i].TA.shape[1])  # identity for an (npair, npair) input
+        if writer is not None:
+            return writer.submit(Fobjs[i].dname, eri)
+        with lock:  # h5py serialises writers anyway
+            file_eri_handler.create_dataset(Fobjs[i].dname, data=eri)
+        return None
 
-    TAs = [np.asfortranarray(f.TA) for f in Fobjs]
-    if precompute_P_mu_nu:
-        exch = ref._get_AO_per_AO(S_abs, AO_coeff_epsilon, None)
-        exch_lists = [np.asarray(exch[mu], dtype=np.int64) for mu in range(mol.nao)]
-        # the reference's own libcint driver fills the host staging view of our tensor
-        P_ref = ref.get_sparse_P_mu_nu(mol, auxmol, exch)
-        build_all_fragments(P_ref.unique_dense_data, (auxmol.nao, mol.nao, mol.nao), exch_lists, L, S_abs, TAs,
-                            MO_coeff_epsilon, locked(sink_for(Fobjs)), devices=devices, whiten=True)
-    else:
-        b = FragmentERIBuilder(devices[0])
-        for i, fobj in enumerate(Fobjs):
-            exch = ref._get_AO_per_AO(S_abs, AO_coeff_epsilon, fobj.TA)
-            P_ref = ref.get_sparse_P_mu_nu(mol, auxmol, exch)
-            exch_lists = [np.asarray(exch[mu], dtype=np.int64) for mu in range(mol.nao)]
-            b.stage(P_ref.unique_dense_data, (auxmol.nao, mol.nao, mol.nao), exch_lists, L, S_abs, whiten=False)
-            b.build(TAs, MO_coeff_epsilon, sink_for(Fobjs), indices=[i])
-        b.close()
+    try:
+        if precompute_P_mu_nu:
+            exch = staging.get_AO_per_AO(S_abs, AO_coeff_epsilon, None)
+            lists = staging.exch_lists(exch, nao)
+            # libcint evaluates every block once; each device receives its own copy
+            tensors = staging.get_sparse_P_mu_nu(mol, auxmol, exch, aux_e2=ref._aux_e2,
+                                                 ctx=[q.default_context(d) for d in devices])
+            build_all_fragments(None, (naux, nao, nao), lists, L, S_abs, TAs, MO_coeff_epsilon, sink, devices=devices,
+                                whiten=True, tensors=tensors)
+        else:
+            b = FragmentERIBuilder(devices[0])
+            metric = q.GPU_MatrixHandle(L, ctx=b.ctx)  # uploaded and block-inverted once, not per fragment
+            screen = q._ScreenHandle(np.asarray(S_abs), b.ctx)
+            for i, fobj in enumerate(Fobjs):
+                exch = staging.get_AO_per_AO(S_abs, AO_coeff_epsilon, fobj.TA)
+                t = staging.get_sparse_P_mu_nu(mol, auxmol, exch, aux_e2=ref._aux_e2, ctx=b.ctx)
+                b.stage(None, None, None, metric, screen, whiten=False, tensor=t)
+                b.build(TAs, MO_coeff_epsilon, sink, indices=[i])
+            b.close()
+    finally:
+        if writer is not None:
+            writer.close()

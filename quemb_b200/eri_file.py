@@ -13,6 +13,10 @@ end-to-end timeline use.  It is a stand-in for the container only; nothing in it
 from __future__ import annotations
 
 import os
+import queue
+import threading
+import time
+from concurrent.futures import Future
 from pathlib import Path
 
 import numpy as np
@@ -71,3 +75,57 @@ def open_eri_file(path, mode: str = "r"):
         return h5py.File(path, mode)
     except ImportError:
         return NpyDirFile(path, mode)
+
+
+class AsyncDatasetWriter:
+    """Background writer between the pinned output ring of the fragment loop and the container
+    (``file_eri_handler.create_dataset(fobj.dname, data=eri)``, ``eri_sparse_DF.py:631``).
+
+    ``submit(name, data)`` returns a ``concurrent.futures.Future`` immediately; one writer thread performs the
+    ``create_dataset`` calls in submission order (h5py serialises writers anyway, SURVEY 8b "Threading").  The
+    fragment loop (``FragmentERIBuilder.build``) treats a Future returned by its sink as "this pinned buffer is still
+    being read" and does not hand the buffer back to the device before it is done, so ``data`` may be a view of the
+    pinned ring: no extra host copy of the ``npair^2`` matrix is made, and the disk write of fragment f overlaps the
+    kernels and the device->host copy of fragments f+1, f+2."""
+
+    def __init__(self, file_handler, max_pending: int = 4):
+        self._fh = file_handler
+        self._q: queue.Queue = queue.Queue(maxsize=max_pending)
+        self.bytes_written = 0
+        self.busy_s = 0.0
+        self._thread = threading.Thread(target=self._run, name="qemb-eri-writer", daemon=True)
+        self._thread.start()
+
+    def _run(self) -> None:
+        while True:
+            item = self._q.get()
+            if item is None:
+                return
+            name, data, fut = item
+            if not fut.set_running_or_notify_cancel():
+                continue
+            try:
+                t0 = time.perf_counter()
+                self._fh.create_dataset(name, data=data)
+                self.busy_s += time.perf_counter() - t0
+                self.bytes_written += int(getattr(data, "nbytes", 0))
+                fut.set_result(name)
+            except BaseException as e:  # noqa: BLE001
+                fut.set_exception(e)
+
+    def submit(self, name: str, data: np.ndarray) -> Future:
+        fut: Future = Future()
+        self._q.put((name, data, fut))
+        return fut
+
+    def close(self) -> None:
+        """Flush: returns when every submitted dataset has been written (errors surface through the futures)."""
+        if self._thread.is_alive():
+            self._q.put(None)
+            self._thread.join()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

@@ -38,17 +38,17 @@ __all__ = [
 
 logger = logging.getLogger(__name__)
 
-_LOG_LEVEL = logging.WARNING
-
-
 def set_log_level(log_level: int) -> None:
-    """``indexers.hpp:43-46``: the level mirrors Python's logging levels."""
-    global _LOG_LEVEL
-    _LOG_LEVEL = int(log_level)
+    """``indexers.hpp:43-46`` / ``pyi:139-157``: process-global level with Python's logging values (the reference
+    driver forwards the root logger's level, ``eri_sparse_DF.py:605``).  At ``<= logging.INFO`` every
+    ``transform_integral`` prints the reference's ``[TIMER] <step> finished in <t> s`` lines (``indexers.hpp:170-204``)
+    from CUDA-event times of screening, K1, K2a, K2b and K3."""
+    check(lib().qemb_set_log_level(c_int(int(log_level))))
 
 
 def get_log_level() -> int:
-    return _LOG_LEVEL
+    """``indexers.hpp:37-40``; default ``logging.ERROR`` like the reference's ``LOG_LEVEL``."""
+    return int(lib().qemb_get_log_level())
 
 
 def _f64(a, name: str) -> np.ndarray:
@@ -116,10 +116,28 @@ class Context:
         check(lib().qemb_ctx_transfer_bytes(self._h, ctypes.byref(a), ctypes.byref(b)))
         return a.value, b.value
 
+    def stream_handoff(self, external_stream: int, direction: int = 0) -> None:
+        """Order an external CUDA stream (``torch.cuda.current_stream().cuda_stream``) against the compute stream
+        without a host synchronisation: ``direction=0`` the external stream waits for the library's enqueued work,
+        ``direction=1`` the library waits for the external stream (``qemb_ctx_stream_handoff``)."""
+        check(lib().qemb_ctx_stream_handoff(self._h, c_p(int(external_stream)), c_int(direction)))
+
     def probe_dmma_tflops(self, n: int = 4096, k: int = 2048, iters: int = 5) -> float:
         v = c_dbl()
         check(lib().qemb_probe_dmma_tflops(self._h, c_i64(n), c_i64(k), c_int(iters), ctypes.byref(v)))
         return v.value
+
+
+def host_bandwidth(nbytes: int = 1 << 30) -> tuple[float, float]:
+    """(write GB/s, copy GB/s) of host DRAM as the library's host threads see it (``qemb_host_bandwidth``)."""
+    w, c = c_dbl(), c_dbl()
+    check(lib().qemb_host_bandwidth(c_i64(int(nbytes)), ctypes.byref(w), ctypes.byref(c)))
+    return float(w.value), float(c.value)
+
+
+def output_ring_depth() -> int:
+    """Host-output transforms that may be pending per workspace (``qemb_output_ring_depth``)."""
+    return int(lib().qemb_output_ring_depth())
 
 
 _CTX: dict[int, Context] = {}
@@ -179,6 +197,18 @@ class Workspace:
         vj, vk = np.empty((n, n), order="F"), np.empty((n, n), order="F")
         check(lib().qemb_fragment_jk(self._h, ptr(D), c_i64(_ld(D)), ptr(vj), ptr(vk), c_i64(n)))
         return vj, vk
+
+    def jk_enqueue(self, dm: np.ndarray, vj: np.ndarray, vk: np.ndarray) -> None:
+        """:meth:`jk` enqueued on the compute stream (``qemb_fragment_jk_enqueue``): ``vj`` / ``vk`` are caller-owned
+        ``(nmo, nmo)`` Fortran-ordered (ideally pinned) arrays that are complete after ``ctx.synchronize()``."""
+        D = _f64(dm, "dm")
+        n = D.shape[0]
+        if D.shape[0] != D.shape[1]:
+            raise _lib.QembError("dm must be square")
+        for a in (vj, vk):
+            if a.shape != (n, n) or a.dtype != np.float64 or not a.flags.f_contiguous:
+                raise _lib.QembError("vj / vk must be (nmo, nmo) float64 Fortran-ordered arrays")
+        check(lib().qemb_fragment_jk_enqueue(self._h, ptr(D), c_i64(_ld(D)), ptr(vj), ptr(vk), c_i64(n)))
 
     def jk_time(self) -> tuple[float, float]:
         """(device ms, algorithmic bytes) of the last :meth:`jk`."""
@@ -340,6 +370,7 @@ class SemiSparseSym3DTensor:
         self._n_unique = n.value
         self._host_mirror: np.ndarray | None = None
         self._dirty = False
+        self._has_device_data = False
         if data is not None:
             d = _f64(data, "unique_dense_data")
             if d.shape != (naux, self._n_unique):
@@ -353,6 +384,14 @@ class SemiSparseSym3DTensor:
         d = _f64(data, "data")
         check(lib().qemb_tensor_upload(self._h, ptr(d), c_i64(d.strides[1] // 8 if d.shape[1] > 1 else d.shape[0]),
                                        c_i64(col0), c_i64(d.shape[1])))
+        self._has_device_data = True
+        if d is not self._host_mirror:
+            self._device_changed()
+
+    def set_whitened(self, flag: bool) -> None:
+        """Declare the device data whitened / raw (``qemb_tensor_set_whitened``): before re-uploading raw columns into
+        a tensor that was whitened, or after a distributed whitening."""
+        check(lib().qemb_tensor_set_whitened(self._h, c_int(1 if flag else 0)))
 
     def scatter_block(self, integrals: np.ndarray, p0: int, q0: int) -> None:
         """Device-side replacement of the Python scatter loop of ``get_sparse_P_mu_nu``
@@ -364,27 +403,58 @@ class SemiSparseSym3DTensor:
         if a.ndim != 3 or a.shape[2] != self._shape[0]:
             raise _lib.QembError("integrals must have shape (n_i, n_j, naux)")
         check(lib().qemb_tensor_scatter_block(self._h, ptr(a), c_i64(a.shape[0]), c_i64(a.shape[1]), c_i64(p0), c_i64(q0)))
+        self._has_device_data = True
+        self._device_changed()
 
     def _flush(self) -> None:
+        """Make the device copy current.  The host mirror handed out by :attr:`mut_unique_dense_data` stays alive
+        (the reference returns a live view, ``cpp:810-812``): later accesses return the same array and later
+        flushes upload it again."""
         if self._dirty and self._host_mirror is not None:
-            self.upload(self._host_mirror)
             self._dirty = False
-            self._host_mirror = None  # the device copy is the tensor from here on
+            self.upload(self._host_mirror)
+
+    def _device_changed(self) -> None:
+        """The device data were modified behind the host mirror (whiten, block staging, upload): the next access to
+        :attr:`mut_unique_dense_data` downloads a fresh copy instead of resurrecting stale (or NaN) values."""
+        self._host_mirror = None
+        self._dirty = False
+
+    def release_host_mirror(self) -> None:
+        """Drop the host staging copy (after a final flush); the device copy is the tensor from here on."""
+        self._flush()
+        self._device_changed()
 
     @property
     def mut_unique_dense_data(self) -> np.ndarray:
-        """Writable host staging area (NaN-filled like ``cpp:160``); uploaded on first device use."""
+        """Writable host view (``pyi:104-110``): NaN-filled like ``cpp:160`` for a fresh tensor, otherwise the
+        current device content; writes reach the device at the next device use.  Re-read the property for every
+        batch of writes (the reference driver does, ``eri_sparse_DF.py:486-488``): a view kept across a device use
+        and written afterwards is only picked up at the next property access."""
         if self._host_mirror is None:
-            self._host_mirror = np.full((self._shape[0], self._n_unique), np.nan, order="F")
+            if self._has_device_data:
+                self._host_mirror = self._download()
+            else:
+                self._host_mirror = np.full((self._shape[0], self._n_unique), np.nan, order="F")
         self._dirty = True
         return self._host_mirror
+
+    def _download(self) -> np.ndarray:
+        out = np.empty((self._shape[0], self._n_unique), order="F")
+        check(lib().qemb_tensor_download(self._h, ptr(out), c_i64(self._shape[0]), c_i64(0), c_i64(self._n_unique)))
+        return out
+
+    def count_nan(self) -> int:
+        """NaN entries left on the device (``qemb_tensor_count_nan``; the reference's post-staging assert, ``py:492``)."""
+        self._flush()
+        n = c_i64()
+        check(lib().qemb_tensor_count_nan(self._h, ctypes.byref(n)))
+        return n.value
 
     @property
     def unique_dense_data(self) -> np.ndarray:
         self._flush()
-        out = np.empty((self._shape[0], self._n_unique), order="F")
-        check(lib().qemb_tensor_download(self._h, ptr(out), c_i64(self._shape[0]), c_i64(0), c_i64(self._n_unique)))
-        return out
+        return self._download()
 
     def __getitem__(self, key: tuple[int, int]) -> np.ndarray:
         mu, nu = key
@@ -401,6 +471,7 @@ class SemiSparseSym3DTensor:
         self._flush()
         m = _metric_for(L_PQ, self.ctx)
         check(lib().qemb_tensor_whiten(self._h, m._h))
+        self._device_changed()
 
     @classmethod
     def whitened_slab(cls, unique_dense_data: np.ndarray, shape, exch_reachable, L_PQ, p_range: tuple[int, int],
@@ -426,6 +497,7 @@ class SemiSparseSym3DTensor:
             check(lib().qemb_tensor_upload_whitened_rows(t._h, m._h, c_p(d.ctypes.data + 8 * ld * c0), c_i64(ld),
                                                          c_i64(c0), c_i64(nc), c_i64(p0)))
         check(lib().qemb_tensor_release_scratch(t._h))
+        t._has_device_data = True
         t.p_range = (p0, p1)
         return t
 
@@ -460,11 +532,15 @@ class SemiSparseSym3DTensor:
             w.wait()
         torch.cuda.current_stream(self.ctx.device).synchronize()
         check(lib().qemb_tensor_set_whitened(self._h, c_int(1)))
+        self._has_device_data = True
+        self._device_changed()
 
     def copy_data_from(self, other: "SemiSparseSym3DTensor") -> None:
         """Device-to-device copy of the data of a tensor built from the same lists."""
         other._flush()
         check(lib().qemb_tensor_copy_data(self._h, other._h))
+        self._has_device_data = other._has_device_data
+        self._device_changed()
 
     @property
     def whitened(self) -> bool:

@@ -94,18 +94,25 @@ class AuxShardedBuilder:
         npair = nmo * (nmo + 1) // 2
         G = self._buffer(k, npair * npair)
         q.transform_integral_device(self.tensor, TA, self.screen, None, eps, G.data_ptr(), npair, ws=self.ws)
-        self.ctx.synchronize()  # the collective runs on torch's stream: hand over a finished buffer
-        return G
+        return G  # enqueued only: _before_collective orders torch's stream behind it, no host synchronisation
+
+    def _torch_stream(self) -> int:
+        import torch
+
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _before_collective(self) -> None:
+        """The collective is enqueued on torch's stream: make that stream wait (on the device) for the kernels the
+        library has enqueued so far -- a CUDA event, not the per-fragment ``ctx.synchronize()`` of round 1."""
+        self.ctx.stream_handoff(self._torch_stream(), 0)
 
     def _to_host(self, G, npair: int) -> np.ndarray:
         return G.cpu().numpy().reshape(npair, npair)
 
     def _collective_done(self) -> None:
-        """NCCL's ``work.wait()`` only orders torch's stream after the collective; the library writes the
-        next partial on its own stream, so the host waits for torch's stream before the buffer is reused."""
-        import torch
-
-        torch.cuda.current_stream(self.device).synchronize()
+        """NCCL's ``work.wait()`` orders torch's stream after the collective; the library writes the next partial
+        into the same buffer on its own stream, so that stream is made to wait for torch's (event, no host sync)."""
+        self.ctx.stream_handoff(self._torch_stream(), 1)
 
     # -- orchestration ----------------------------------------------------------------------------------
     def stage(self, unique_dense_data, shape, exch_reachable, L_PQ, S_abs) -> None:
@@ -129,6 +136,7 @@ class AuxShardedBuilder:
             G = self._partial(k, TA, MO_coeff_epsilon)
             if pending is not None:
                 self._finish(pending, sink, owned)
+            self._before_collective()
             work = self.dist.reduce(G, dst=self._global_rank(owner_of(k, self.world)), op=self.dist.ReduceOp.SUM,
                                     group=self.group, async_op=True)
             pending = (work, k, i, G, npair)
@@ -144,11 +152,11 @@ class AuxShardedBuilder:
     def _finish(self, pending, sink: Sink | None, owned: list[int]) -> None:
         work, k, i, G, npair = pending
         work.wait()
-        self._collective_done()
         if owner_of(k, self.world) == self.rank:
             owned.append(i)
             if sink is not None:
-                sink(i, self._to_host(G, npair))
+                sink(i, self._to_host(G, npair))  # reads on torch's stream, behind the collective
+        self._collective_done()
 
 
 class FusedAuxShardedBuilder(AuxShardedBuilder):
@@ -162,7 +170,9 @@ class FusedAuxShardedBuilder(AuxShardedBuilder):
     the owner that all contributions have landed, and the owner rebuilds the upper triangle on the device
     (``qemb_device_mirror_lower``).  The matrices are plain ``cudaMalloc`` buffers shared with ``cudaIpc*`` handles,
     exchanged once through ``all_gather_object``.  The sum order inside a tile entry depends on arrival order for
-    more than two ranks (atomics): results agree with the unsharded path to the 1e-10 budget, not bit for bit.
+    more than two ranks (atomics): results agree with the unsharded path to the 1e-10 budget, not bit for bit, and
+    are NOT run-to-run reproducible beyond two ranks.  This variant is therefore OPT-IN; the default and the one
+    ``bench.py`` reports is :class:`AuxShardedBuilder` (NCCL ``reduce``, fixed reduction tree, deterministic).
     """
 
     def __init__(self, dist, device: int = 0, group=None):

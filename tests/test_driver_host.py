@@ -142,6 +142,8 @@ class CpuSlabBuilder(AuxShardedBuilder):
         return G.numpy().reshape(npair, npair)
     def _collective_done(self):
         pass
+    def _before_collective(self):
+        pass
 
 dist.init_process_group("gloo")
 rank, world = dist.get_rank(), dist.get_world_size()
