@@ -42,3 +42,32 @@ def ebe_hf_two_electron(ws: Workspace, rdm_hf: np.ndarray, n_frag: int) -> np.nd
     D = np.asarray(rdm_hf, dtype=np.float64)
     vj, vk = ws.jk(0.5 * (D + D.T))
     return np.einsum("ij,ij->i", D[:n_frag], 2.0 * vj[:n_frag] - vk[:n_frag])
+
+
+def initialize_fragments(builder, TAs, MO_coeff_epsilon: float, hf_dm: np.ndarray, S: np.ndarray,
+                         hf_veff: np.ndarray, rdm_hfs, n_frags, indices=None) -> dict[int, dict]:
+    """The ERI-consuming part of ``BE.initialize`` (``mbe.py:1146-1170``) for ALL fragments in one device-resident
+    pass: per fragment the transform leaves (ij|kl) in HBM and two J/K contractions are enqueued right behind it
+    (``FragmentERIBuilder.build_jk``) -- ``get_veff`` for ``cons_fock`` (``helper.py:28-69``) and the two-electron
+    sum of ``update_ebe_hf`` (``pfrag.py:368-389``) for the densities ``rdm_hfs[i]`` -- so only ``nmo x nmo``
+    matrices leave the device and no ``eri_file`` round trip is needed.  ``builder`` is a staged
+    :class:`quemb_b200.driver.FragmentERIBuilder`.  Returns ``{i: {"veff", "veff0", "e2", "vj", "vk"}}``."""
+    idx = list(range(len(TAs))) if indices is None else list(indices)
+    STs = {i: S @ TAs[i] for i in idx}
+
+    def densities(i):
+        P_ = np.asarray((STs[i].T @ hf_dm @ STs[i]).real, dtype=np.float64)
+        D = np.asarray(rdm_hfs[i], dtype=np.float64)
+        return [0.5 * (P_ + P_.T), 0.5 * (D + D.T)]
+
+    jk = builder.build_jk(TAs, MO_coeff_epsilon, densities, indices=idx)
+    out = {}
+    for i in idx:
+        (vj, vk), (vj2, vk2) = jk[i]
+        TA = TAs[i]
+        veff0 = TA.T @ hf_veff @ TA
+        D = np.asarray(rdm_hfs[i], dtype=np.float64)
+        n = int(n_frags[i])
+        out[i] = {"veff": veff0 - (vj - 0.5 * vk), "veff0": veff0, "vj": vj, "vk": vk,
+                  "e2": np.einsum("ij,ij->i", D[:n], 2.0 * vj2[:n] - vk2[:n])}
+    return out

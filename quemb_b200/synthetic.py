@@ -275,3 +275,42 @@ def c32h66_like(seed: int = SEED, n_frag: int | None = None, matmul=None) -> Pro
         n_units=32, ao_per_unit=24, n_end=5, naux=2716, frag_halfwidth=2,
         n_bath=100, seed=seed, n_frag=n_frag, name="C32H66-like", matmul=matmul,
     )
+
+
+# Throughput-sweep points and oversize fragments (BASELINE.json configs[3], configs[4]) ----------------------
+
+def _fit_sigma(r: np.ndarray, naux: int, max_bytes: float, sigma: float, shrink: float = 0.85, floor: float = 0.2) -> float:
+    """Largest sigma (from the start value down) whose screened (P|mu nu) fits ``max_bytes`` of host memory: the
+    sweep and the oversize cases measure the fragment kernels, not host-side generation."""
+    d2 = ((r[:, None, :] - r[None, :, :]) ** 2).sum(-1)
+    while True:
+        nu = int(np.tril(np.exp(-d2 / (2.0 * sigma * sigma)) >= 1e-10).sum())
+        if nu * naux * 8 <= max_bytes or sigma < floor:
+            return sigma
+        sigma *= shrink
+
+
+def sweep_point(nmo: int, naux: int, max_bytes: float = 3e9, matmul=None, cond: float = 1e8) -> Problem:
+    """One point of the synthetic sweep (SURVEY 8d "sweep": nmo in 20..400 x naux in 500..8000, nao ~ 4 nmo, one
+    fragment): a chain whose interior fragment (``TAs[-1]``) has 3 units (55 % of nmo) + bath tails (45 %)."""
+    a = max(2, round(0.55 * nmo / 3))
+    n_bath = max(1, nmo - 3 * a)
+    n_units = max(5, round(4 * nmo / a))
+    sigma = _fit_sigma(chain_centres(n_units, a, 0, np.random.default_rng(1)), naux, max_bytes, 0.94)
+    p = make_chain_problem(n_units=n_units, ao_per_unit=a, n_end=0, naux=naux, frag_halfwidth=1, n_bath=n_bath,
+                           sigma=sigma, cond=cond, seed=SEED + nmo + naux, n_frag=n_units // 2 + 1, matmul=matmul,
+                           name=f"sweep nmo{nmo} naux{naux}")
+    p.meta["sigma"] = sigma
+    return p
+
+
+def h2o64_like(n_side: int = 4, naux: int = 9024, n_frag: int = 1, max_bytes: float = 6e9, matmul=None,
+               n_sites: int = 4, n_bath: int = 100) -> Problem:
+    """(H2O)64-like 3-D lattice (BASELINE.json configs[3]): ``n_side^3`` sites x 58 AOs (cc-pVTZ water), fragments of
+    ``n_sites`` sites + ``n_bath`` bath orbitals (nmo 332 by default).  ``n_side=4, naux=9024`` is the full-size case
+    (nao 3712); smaller ``n_side`` / ``naux`` keep nmo and shrink the environment so that a CPU oracle finishes."""
+    sigma = _fit_sigma(lattice_centres(n_side, 58, np.random.default_rng(7)), naux, max_bytes, 0.6, shrink=0.9, floor=0.1)
+    p = make_lattice_problem(n_side=n_side, ao_per_site=58, naux=naux, n_frag=max(n_frag, 1), n_bath=n_bath, sigma=sigma,
+                             cond=1e8, seed=SEED + 64, name="(H2O)64-like", matmul=matmul, n_sites=n_sites)
+    p.meta["sigma"] = sigma
+    return p

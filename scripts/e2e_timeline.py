@@ -1,49 +1,140 @@
-"""Development aid: where the wall time of one end-to-end build goes (host view).
-usage: python scripts/e2e_timeline.py [triangle=1] [n_host_buffers=3] [nfrag=32]"""
-import sys, time
+"""Where the wall time of one end-to-end build goes, per rank (host view), at N = 1 / 2 / 4 / 8.
+
+  python scripts/e2e_timeline.py [--output triangle|full] [--upload replicated|sharded] [--reps 3]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 scripts/e2e_timeline.py ...
+
+Per rank and repetition: upload (host -> device of (P|mu nu)), stage (L, S_abs, metric application incl. the NCCL
+exchange), build (all of the rank's fragments, every full (ij|kl) in pinned host memory), split into the time the
+host spent enqueueing transforms, waiting for outputs and inside the sink; bytes over PCIe both ways; the host's
+DRAM bandwidth with the rank's own pool threads.  Rank 0 gathers everything and appends one JSON line to --out.
+"""
+import argparse
+import json
+import os
+import sys
+import time
 from pathlib import Path
+
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np
-import bench
-from quemb_b200 import eri_sparse_DF as q
-from quemb_b200.driver import FragmentERIBuilder
 
-tri = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-nb = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-nfrag = int(sys.argv[3]) if len(sys.argv) > 3 else 32
-frac = float(sys.argv[4]) if len(sys.argv) > 4 else 0.0
-p = bench.make_workload("c32h66", use_gpu_matmul=True)
-idx = list(range(len(p.TAs)))[:nfrag]
-b = FragmentERIBuilder(0, n_host_buffers=nb)
-ctx = b.ctx
-ctx.set_output_mode(bool(tri))
-ctx.set_full_column_fraction(frac)
-T = q.SemiSparseSym3DTensor((p.naux, p.nao, p.nao), p.exch_reachable, ctx=ctx)
-b.reserve_host(max(t.shape[1] for t in p.TAs))
-log = []
-orig_t, orig_w = q.transform_integral, b.ws.wait_output
-def timed_t(*a, **k):
-    t = time.perf_counter(); r = orig_t(*a, **k); log.append(("enqueue", time.perf_counter() - t)); return r
-def timed_w(ticket):
-    t = time.perf_counter(); r = orig_w(ticket); log.append(("wait", time.perf_counter() - t)); return r
-q.transform_integral = timed_t; b.ws.wait_output = timed_w
-chk = []
-def sink(i, G):
-    t = time.perf_counter(); chk.append(float(G[0, 0]) + float(G[-1, 0]) + float(G[0, -1])); log.append(("sink", time.perf_counter() - t))
-for rep in range(3):
-    log.clear()
-    t0 = time.perf_counter()
-    T.upload(p.unique_dense_data); ctx.synchronize(); t1 = time.perf_counter()
-    b.stage(None, None, None, p.L_PQ, p.S_abs, whiten=True, tensor=T); ctx.synchronize(); t2 = time.perf_counter()
-    b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=idx); ctx.synchronize(); t3 = time.perf_counter()
-    tot = {}
-    for k, v in log: tot[k] = tot.get(k, 0) + v
-    d2h = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in idx)
-    print(f"rep {rep} tri={tri} nb={nb} full_frac={frac}: upload {t1-t0:.3f} stage+whiten {t2-t1:.3f} build {t3-t2:.3f} total {t3-t0:.3f} s | "
-          + " ".join(f"{k} {v:.3f}" for k, v in tot.items()) + f" | G bytes {d2h/1e9:.1f} GB -> {d2h/(t3-t2)/1e9:.1f} GB/s effective")
-# symmetry / parity spot check of the last fragment against the full-square mode
-i = idx[-1]; nmo = p.TAs[i].shape[1]; npair = nmo * (nmo + 1) // 2
-G1 = np.array(q.transform_integral(T, p.TAs[i], b.screen, None, p.MO_coeff_epsilon, ws=b.ws))
-ctx.set_output_mode(False)
-G0 = np.array(q.transform_integral(T, p.TAs[i], b.screen, None, p.MO_coeff_epsilon, ws=b.ws))
-print("triangle-vs-full max abs diff", float(np.abs(G1 - G0).max()), "symmetric", bool(np.array_equal(G1, G1.T)))
+import bench
+from quemb_b200 import _lib
+from quemb_b200 import eri_sparse_DF as q
+from quemb_b200.driver import FragmentERIBuilder, fragment_cost, partition_lpt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--output", default="triangle", choices=["triangle", "full"])
+    ap.add_argument("--upload", default="sharded", choices=["replicated", "sharded"])
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--buffers", type=int, default=3)
+    ap.add_argument("--out", default="gpurun_out/e2e_timeline.jsonl")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    p = bench.make_workload("c32h66", use_gpu_matmul=True)
+    costs = [fragment_cost(p.naux, t.shape[1]) for t in p.TAs]
+    mine = partition_lpt(costs, world)[rank]
+    b = FragmentERIBuilder(local, n_host_buffers=args.buffers)
+    ctx = b.ctx
+    ctx.set_output_mode(args.output == "triangle")
+    T = q.SemiSparseSym3DTensor((p.naux, p.nao, p.nao), p.exch_reachable, ctx=ctx)
+    b.reserve_host(max(t.shape[1] for t in p.TAs))
+    hw, hc = q.host_bandwidth(1 << 30)
+
+    log = {}
+    orig_t, orig_w = q.transform_integral, b.ws.wait_output
+
+    def timed(name, fn):
+        def f(*a, **k):
+            t = time.perf_counter()
+            r = fn(*a, **k)
+            log[name] = log.get(name, 0.0) + time.perf_counter() - t
+            return r
+        return f
+
+    q.transform_integral = timed("enqueue_s", orig_t)
+    b.ws.wait_output = timed("wait_s", orig_w)
+    chk = []
+
+    def sink(i, G):
+        t = time.perf_counter()
+        chk.append(float(G[0, 0]) + float(G[-1, 0]) + float(G[0, -1]))
+        log["sink_s"] = log.get("sink_s", 0.0) + time.perf_counter() - t
+
+    rows = []
+    for rep in range(args.reps + 1):
+        log.clear()
+        barrier()
+        x0 = ctx.transfer_bytes
+        t0 = time.perf_counter()
+        if world == 1 or args.upload == "replicated":
+            T.upload(p.unique_dense_data)
+            ctx.synchronize()
+            t1 = time.perf_counter()
+            b.stage(None, None, None, p.L_PQ, p.S_abs, whiten=False, tensor=T)
+            if dist is None:
+                T.whiten(b.metric)
+            else:
+                T.whiten_distributed(b.metric, dist)
+        else:
+            t1 = t0
+            b.stage_distributed(p.unique_dense_data, p.L_PQ, p.S_abs, dist, tensor=T)
+        ctx.synchronize()
+        t2 = time.perf_counter()
+        b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
+        ctx.synchronize()
+        t3 = time.perf_counter()
+        barrier()
+        t4 = time.perf_counter()
+        x1 = ctx.transfer_bytes
+        if rep == 0:
+            continue  # warm-up
+        res = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in mine)
+        rows.append({"rep": rep, "upload_s": t1 - t0, "stage_s": t2 - t1, "build_s": t3 - t2, "total_s": t3 - t0,
+                     "all_ranks_done_s": t4 - t0, **{k: v for k, v in log.items()},
+                     "h2d_gb": (x1[0] - x0[0]) / 1e9, "d2h_gb": (x1[1] - x0[1]) / 1e9, "result_gb": res / 1e9,
+                     "delivery_gbs": res / (t3 - t2) / 1e9})
+    mean = {k: float(np.mean([r[k] for r in rows])) for k in rows[0] if k != "rep"}
+    mine_rec = {"rank": rank, "fragments": len(mine), "host_threads": bench.q_host_threads(_lib),
+                "host_write_gbs_rank_threads": hw, "host_copy_gbs_rank_threads": hc, "mean": mean, "reps": rows}
+    allrec = [mine_rec]
+    if dist is not None:
+        allrec = [None] * world
+        dist.all_gather_object(allrec, mine_rec)
+    if rank == 0:
+        line = {"n_gpus": world, "output": args.output, "upload": args.upload, "buffers": args.buffers,
+                "cores": len(os.sched_getaffinity(0)),
+                "e2e_s_max_over_ranks": max(r["mean"]["total_s"] for r in allrec),
+                "all_ranks_done_s": max(r["mean"]["all_ranks_done_s"] for r in allrec),
+                "result_gb_total": sum(r["mean"]["result_gb"] for r in allrec),
+                "ranks": allrec}
+        line["aggregate_delivery_gbs"] = line["result_gb_total"] / line["e2e_s_max_over_ranks"]
+        Path(args.out).parent.mkdir(parents=True, exist_ok=True)
+        with open(args.out, "a") as f:
+            f.write(json.dumps(line) + "\n")
+        brief = {k: v for k, v in line.items() if k != "ranks"}
+        brief["rank0_mean"] = allrec[0]["mean"]
+        print(json.dumps(brief), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -46,24 +46,9 @@ def gpu_matmul(A, B):
 
 
 def make_point(nmo: int, naux: int, max_bytes: float):
-    """Chain with nao ~ 4 nmo; the fragment = 3 units (55 % of nmo) + bath tails (45 %).  sigma is reduced
-    until (P|mu nu) fits `max_bytes` (the sweep measures the fragment kernels, not host generation)."""
-    a = max(2, round(0.55 * nmo / 3))
-    n_bath = max(1, nmo - 3 * a)
-    n_units = max(5, round(4 * nmo / a))
-    sigma = 0.94
-    while True:
-        rng = np.random.default_rng(1)
-        r = syn.chain_centres(n_units, a, 0, rng)
-        S = syn.gaussian_S_abs(r, sigma)
-        nu = int((np.tril(S >= 1e-10)).sum())
-        if nu * naux * 8 <= max_bytes or sigma < 0.2:
-            break
-        sigma *= 0.85
-    p = syn.make_chain_problem(n_units=n_units, ao_per_unit=a, n_end=0, naux=naux, frag_halfwidth=1, n_bath=n_bath,
-                               sigma=sigma, cond=1e8, seed=syn.SEED + nmo + naux, n_frag=n_units // 2 + 1,
-                               matmul=gpu_matmul, name=f"sweep nmo{nmo} naux{naux}")
-    return p, sigma
+    """The shared generator (quemb_b200.synthetic.sweep_point) with the GPU-accelerated L @ Y."""
+    p = syn.sweep_point(nmo, naux, max_bytes, matmul=gpu_matmul)
+    return p, p.meta["sigma"]
 
 
 def main():

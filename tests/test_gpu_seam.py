@@ -1,0 +1,377 @@
+"""The product seam on the GPU (SURVEY rows a2-a4, a14, f2, f3 and the 8b "Threading" contract): device staging of
+(P|mu nu), ``transform_sparse_DF_integral_b200`` driven end to end with stub ``pyscf`` / ``quemb`` modules into an
+``eri_file``, ``build_all_fragments``, the background writer on the pinned ring, concurrent callers, log level."""
+from __future__ import annotations
+
+import logging
+import sys
+import threading
+import types
+
+import numpy as np
+import pytest
+import scipy.linalg
+
+from helpers import GOLDEN, csr_lists
+from test_staging_host import StubMol, stub_aux_e2
+
+pytestmark = pytest.mark.gpu
+
+D = np.load(GOLDEN / "staging_rules.npz")
+
+
+@pytest.fixture(scope="module")
+def q():
+    from quemb_b200 import _lib
+    from quemb_b200 import eri_sparse_DF as mod
+
+    if _lib.device_count() == 0:
+        pytest.skip("no CUDA device")
+    return mod
+
+
+def _oracle():
+    from oracle import oracle
+
+    return oracle
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# a2 / f2: device staging == the reference's get_sparse_P_mu_nu
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", [str(x) for x in D["stage_names"]])
+def test_device_staging_matches_reference_get_sparse_P_mu_nu(q, name):
+    from quemb_b200 import staging
+
+    shells = D[f"{name}/shells"].tolist()
+    src, naux = D[f"{name}/src"], int(D[f"{name}/naux"])
+    lists = csr_lists(D[f"{name}/ptr"], D[f"{name}/idx"])
+    exch = {mu: lists[mu] for mu in range(len(lists)) if D[f"{name}/present"][mu]}
+    mol, auxmol = StubMol(shells), StubMol([4] * (naux // 4))
+    T = staging.get_sparse_P_mu_nu(mol, auxmol, exch, aux_e2=stub_aux_e2(src))
+    assert T.count_nan() == 0
+    assert np.array_equal(T.unique_dense_data, D[f"{name}/M"])  # bit-exact: staging only moves bytes
+    # a tensor nobody filled reports its NaNs (the reference's assert, py:492)
+    T2 = q.SemiSparseSym3DTensor((naux, mol.nao, mol.nao), staging.exch_lists(exch, mol.nao))
+    assert T2.count_nan() == naux * T2._n_unique
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# a14: the whole seam with stub pyscf / quemb modules
+# ------------------------------------------------------------------------------------------------------------------
+class _Frag:
+    def __init__(self, TA, i):
+        self.TA, self.dname = TA, f"f{i}"
+
+
+def _seam_problem():
+    from quemb_b200 import synthetic as syn
+
+    p = syn.make_chain_problem(n_units=7, ao_per_unit=9, n_end=2, naux=88, frag_halfwidth=1, n_bath=7, sigma=0.5,
+                               cond=1e4, seed=31)
+    shells = []
+    while sum(shells) < p.nao:
+        shells.append(min((1, 3, 5)[len(shells) % 3], p.nao - sum(shells)))
+    src = np.full((p.nao, p.nao, p.naux), np.nan)  # unscreened pairs must never be copied
+    col = 0
+    for mu, lst in enumerate(p.exch_reachable):
+        for nu in lst:
+            if nu > mu:
+                break
+            src[mu, nu] = src[nu, mu] = p.unique_dense_data[:, col]
+            col += 1
+    assert col == p.n_unique
+    return p, shells, src
+
+
+def _install_stubs(monkeypatch, p, shells, src, calls):
+    PQ = np.tril(p.L_PQ) @ np.tril(p.L_PQ).T
+
+    class Aux(StubMol):
+        def intor(self, name):
+            assert name == "int2c2e"
+            return PQ
+
+    def make_auxmol(mol, auxbasis=None):
+        calls["make_auxmol"] = calls.get("make_auxmol", 0) + 1
+        return Aux([4] * (p.naux // 4))
+
+    def restore(sym, eri, nmo):
+        npair = nmo * (nmo + 1) // 2
+        assert sym == "4" and eri.shape == (npair, npair)  # identity for this input (eri_sparse_DF.py:630)
+        calls["restore"] = calls.get("restore", 0) + 1
+        return eri
+
+    aux_e2 = stub_aux_e2(src)
+
+    def counted_aux_e2(*a, **k):
+        calls["aux_e2"] = calls.get("aux_e2", 0) + 1
+        return aux_e2(*a, **k)
+
+    ref = types.ModuleType("quemb.molbe.eri_sparse_DF")
+    ref.approx_S_abs = lambda mol: p.S_abs
+    ref._aux_e2 = counted_aux_e2
+    mods = {
+        "pyscf": types.ModuleType("pyscf"), "pyscf.ao2mo": types.ModuleType("pyscf.ao2mo"),
+        "pyscf.ao2mo.addons": types.ModuleType("pyscf.ao2mo.addons"), "pyscf.df": types.ModuleType("pyscf.df"),
+        "pyscf.df.addons": types.ModuleType("pyscf.df.addons"), "quemb": types.ModuleType("quemb"),
+        "quemb.molbe": types.ModuleType("quemb.molbe"), "quemb.molbe.eri_sparse_DF": ref,
+    }
+    mods["pyscf.ao2mo.addons"].restore = restore
+    mods["pyscf.df.addons"].make_auxmol = make_auxmol
+    mods["quemb.molbe"].eri_sparse_DF = ref
+    for k, v in mods.items():
+        monkeypatch.setitem(sys.modules, k, v)
+    mf = types.SimpleNamespace(mol=StubMol(shells))
+    L_used = scipy.linalg.cholesky(PQ, lower=True)  # what the seam computes from int2c2e (eri_sparse_DF.py:612-613)
+    return mf, L_used
+
+
+@pytest.mark.parametrize("precompute", [True, False])
+@pytest.mark.parametrize("async_write", [True, False])
+def test_seam_writes_every_fragment_dataset(q, monkeypatch, tmp_path, precompute, async_write):
+    """``transform_sparse_DF_integral_b200`` for both ``precompute_P_mu_nu`` values into ``open_eri_file``; every
+    ``f{i}`` is read back and compared with the oracle on the lists the reference would have used."""
+    from quemb_b200 import staging
+    from quemb_b200.driver import transform_sparse_DF_integral_b200
+    from quemb_b200.eri_file import open_eri_file
+
+    oracle = _oracle()
+    p, shells, src = _seam_problem()
+    calls: dict = {}
+    mf, L_used = _install_stubs(monkeypatch, p, shells, src, calls)
+    Fobjs = [_Frag(np.array(TA, order="C"), i) for i, TA in enumerate(p.TAs)]  # QuEmb hands C-ordered TA
+    path = tmp_path / "eri_file.h5"
+    with open_eri_file(path, "w") as fh:
+        transform_sparse_DF_integral_b200(mf, Fobjs, "stub-ri", fh, p.AO_coeff_epsilon, p.MO_coeff_epsilon,
+                                          n_threads=1, precompute_P_mu_nu=precompute, async_write=async_write)
+    assert calls["restore"] == len(Fobjs) and calls["make_auxmol"] == 1 and calls["aux_e2"] > 0
+    worst = 0.0
+    with open_eri_file(path, "r") as fh:
+        for i, f in enumerate(Fobjs):
+            got = np.array(fh.get(f.dname))
+            nmo = f.TA.shape[1]
+            assert got.dtype == np.float64 and got.shape == (nmo * (nmo + 1) // 2,) * 2
+            if precompute:
+                lists, M = p.exch_reachable, p.unique_dense_data
+            else:  # on-the-fly: per-fragment sources (py:634-637); a partial dict, missing keys = empty lists
+                exch = staging.get_AO_per_AO(p.S_abs, p.AO_coeff_epsilon, f.TA)
+                assert len(exch) < p.nao or i in (2, 3, 4)
+                lists = staging.exch_lists(exch, p.nao)
+                cols = [src[mu, nu] for mu, lst in enumerate(lists) for nu in lst if nu <= mu]
+                M = np.asfortranarray(np.array(cols).T)
+            want = oracle.transform_integral(M, lists, f.TA, p.S_abs, L_used, p.MO_coeff_epsilon)
+            worst = max(worst, float(np.abs(got - want).max()))
+            assert np.array_equal(got, got.T)
+    assert worst <= 1e-10, worst
+
+
+def test_build_all_fragments_one_thread_per_device(q):
+    """``build_all_fragments`` (dynamic queue, one thread per device) on device 0, and on (0, 1) when present."""
+    from quemb_b200 import _lib, synthetic as syn
+    from quemb_b200.driver import build_all_fragments
+
+    oracle = _oracle()
+    p = syn.make_chain_problem(n_units=8, ao_per_unit=8, n_end=2, naux=120, frag_halfwidth=1, n_bath=8, sigma=0.6, seed=33)
+    for devices in ((0,), (0, 1)):
+        if max(devices) >= _lib.device_count():
+            continue
+        got, lock = {}, threading.Lock()
+
+        def sink(i, G):
+            with lock:
+                got[i] = np.array(G)
+
+        build_all_fragments(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs, p.TAs,
+                            p.MO_coeff_epsilon, sink, devices=devices)
+        assert sorted(got) == list(range(len(p.TAs)))
+        for i, TA in enumerate(p.TAs):
+            want = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+            assert np.abs(got[i] - want).max() <= 1e-10
+
+
+def test_background_writer_on_the_pinned_ring(q, tmp_path):
+    """f3: datasets are written by the background thread straight out of the pinned output ring (no host copy); a
+    buffer is only reused once its write is done -- every file content must be its own fragment."""
+    from quemb_b200 import synthetic as syn
+    from quemb_b200.driver import FragmentERIBuilder
+    from quemb_b200.eri_file import AsyncDatasetWriter, open_eri_file
+
+    oracle = _oracle()
+    p = syn.make_chain_problem(n_units=9, ao_per_unit=8, n_end=2, naux=96, frag_halfwidth=1, n_bath=8, sigma=0.6, seed=34)
+    b = FragmentERIBuilder(0, n_host_buffers=2)
+    b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+    with open_eri_file(tmp_path / "e.h5", "w") as fh:
+        with AsyncDatasetWriter(fh) as w:
+            b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: w.submit(f"f{i}", G))
+        assert w.bytes_written == sum(8 * (t.shape[1] * (t.shape[1] + 1) // 2) ** 2 for t in p.TAs)
+    with open_eri_file(tmp_path / "e.h5", "r") as fh:
+        for i, TA in enumerate(p.TAs):
+            want = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+            assert np.abs(np.array(fh[f"f{i}"]) - want).max() <= 1e-10
+    b.close()
+
+
+def test_n_host_buffers_is_clamped_to_the_ring_depth(q, caplog):
+    from quemb_b200 import synthetic as syn
+    from quemb_b200.driver import FragmentERIBuilder
+
+    depth = q.output_ring_depth()
+    assert depth >= 2
+    with caplog.at_level(logging.WARNING):
+        b = FragmentERIBuilder(0, n_host_buffers=depth + 3)
+    assert b._n_host_buffers == depth and "clamped" in caplog.text
+    p = syn.make_chain_problem(n_units=8, ao_per_unit=6, n_end=1, naux=64, frag_halfwidth=1, n_bath=6, sigma=0.5, seed=35)
+    b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+    seen = []
+    b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: seen.append(i))  # no "ticket too old" with a full ring
+    assert seen == list(range(len(p.TAs)))
+    b.close()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# tensor host view / whitened flag
+# ------------------------------------------------------------------------------------------------------------------
+def test_mut_unique_dense_data_survives_a_flush(q):
+    """``mut_unique_dense_data`` is a live view in the reference (``cpp:810-812``): writing, using the tensor on the
+    device, and writing again must not resurrect NaNs over columns that were already uploaded."""
+    from helpers import Golden
+
+    g = Golden("chain_small")
+    T = q.SemiSparseSym3DTensor((g.naux, g.nao, g.nao), g.exch)
+    n = g.M.shape[1]
+    T.mut_unique_dense_data[:, : n // 2] = g.M[:, : n // 2]
+    assert np.isnan(T[(0, 0)]).sum() == 0 or n // 2 == 0      # device use #1: flush
+    T.mut_unique_dense_data[:, n // 2:] = g.M[:, n // 2:]      # second batch of writes after the flush
+    assert np.array_equal(T.unique_dense_data, g.M)
+    # the device copy changed behind the host view (whiten): the next access shows the device content, not stale data
+    T.whiten(g.L)
+    W = T.unique_dense_data
+    v = T.mut_unique_dense_data
+    assert np.array_equal(v, W)
+    fr = g.frag(0)
+    G = q.transform_integral(T, fr["TA"], g.S_abs, None, g.eps)
+    assert np.abs(G - fr["G"]).max() <= 1e-10
+
+
+def test_partial_upload_into_a_whitened_tensor_is_rejected(q):
+    from helpers import Golden
+    from quemb_b200 import _lib
+
+    g = Golden("chain_small")
+    T = q.SemiSparseSym3DTensor(g.M, (g.naux, g.nao, g.nao), g.exch)
+    T.whiten(g.L)
+    with pytest.raises(_lib.QembError, match="whitened"):
+        T.upload(g.M[:, :3], col0=0)
+    with pytest.raises(_lib.QembError, match="whitened"):
+        T.scatter_block(np.zeros((1, 1, g.naux)), 0, 0)
+    assert T.whitened
+    T.upload(g.M)           # a full replacement is fine and clears the flag
+    assert not T.whitened
+    fr = g.frag(1)
+    G = q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps)
+    assert np.abs(G - fr["G"]).max() <= 1e-10
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# 8b "Threading": concurrent callers on distinct workspaces (cpp:889-938, eri_sparse_DF.py:649-653)
+# ------------------------------------------------------------------------------------------------------------------
+def test_two_threads_two_workspaces_share_the_handles(q):
+    from quemb_b200 import synthetic as syn
+
+    oracle = _oracle()
+    p = syn.make_chain_problem(n_units=10, ao_per_unit=8, n_end=2, naux=104, frag_halfwidth=1, n_bath=8, sigma=0.6, seed=36)
+    ctx = q.default_context(0)
+    T = q.SemiSparseSym3DTensor(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, ctx=ctx)
+    Lh = q.GPU_MatrixHandle(p.L_PQ, ctx=ctx)
+    Sh = q._ScreenHandle(p.S_abs, ctx)
+    want = [oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+            for TA in p.TAs]
+    errs, fails = {}, []
+
+    def worker(k):
+        try:
+            ws = q.Workspace(ctx)
+            for rep in range(3):
+                for i in range(k, len(p.TAs), 2):
+                    G = q.transform_integral(T, p.TAs[i], Sh, Lh, p.MO_coeff_epsilon, ws=ws)
+                    errs[(k, rep, i)] = float(np.abs(G - want[i]).max())
+        except BaseException as e:  # noqa: BLE001
+            fails.append(e)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not fails, fails
+    assert len(errs) == 3 * len(p.TAs) and max(errs.values()) <= 1e-10
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# log level / [TIMER] lines (hpp:34-46, 170-204)
+# ------------------------------------------------------------------------------------------------------------------
+def test_info_level_prints_timer_lines(q, capfd):
+    from helpers import Golden
+
+    g = Golden("chain_small")
+    T = q.SemiSparseSym3DTensor(g.M, (g.naux, g.nao, g.nao), g.exch)
+    fr = g.frag(0)
+    assert q.get_log_level() == logging.ERROR  # the reference's default (hpp:34)
+    q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps)
+    assert "[TIMER]" not in capfd.readouterr().out
+    q.set_log_level(logging.INFO)
+    try:
+        assert q.get_log_level() == logging.INFO
+        G = q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps)
+    finally:
+        q.set_log_level(logging.ERROR)
+    out = capfd.readouterr().out
+    for step in ("get_AO_per_MO", "contract_with_TA_1st", "contract_with_TA_2nd_to_sym_dense", "eval_via_cholesky:trsm",
+                 "eval_via_cholesky:gram"):
+        assert f"[TIMER] {step} finished in " in out, out
+    assert np.abs(G - fr["G"]).max() <= 1e-10
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# f1: all-fragment consumer pipeline
+# ------------------------------------------------------------------------------------------------------------------
+def test_build_jk_pipeline_matches_the_consumer_oracle(q):
+    """``FragmentERIBuilder.build_jk``: transform + enqueued J/K per fragment, only nmo x nmo results leave the
+    device; against ``dot_eri_dm`` restated on the oracle's (ij|kl) (helper.py:28-69, pfrag.py:368-389)."""
+    from oracle import consumer_oracle as co
+    from quemb_b200 import consumer, synthetic as syn
+    from quemb_b200.driver import FragmentERIBuilder
+
+    oracle = _oracle()
+    p = syn.make_chain_problem(n_units=8, ao_per_unit=8, n_end=2, naux=112, frag_halfwidth=1, n_bath=8, sigma=0.6, seed=37)
+    rng = np.random.default_rng(5)
+    dms = {}
+    for i, TA in enumerate(p.TAs):
+        n = TA.shape[1]
+        a, b_ = rng.standard_normal((n, n)), rng.standard_normal((n, n))
+        dms[i] = [a + a.T, b_ @ b_.T]
+    b = FragmentERIBuilder(0)
+    b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+    res = b.build_jk(p.TAs, p.MO_coeff_epsilon, lambda i: dms[i])
+    assert sorted(res) == list(range(len(p.TAs)))
+    for i, TA in enumerate(p.TAs):
+        G = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+        for (vj, vk), dm in zip(res[i], dms[i]):
+            wj, wk = co.dot_eri_dm(G, dm)
+            scale = max(1.0, float(np.abs(wj).max()), float(np.abs(wk).max()))
+            assert np.abs(vj - wj).max() <= 1e-10 * scale and np.abs(vk - wk).max() <= 1e-10 * scale
+    # the high-level form: get_veff + ebe_hf two-electron sums for every fragment from one pass
+    S = np.eye(p.nao)
+    hf_dm = rng.standard_normal((p.nao, p.nao))
+    hf_dm = hf_dm + hf_dm.T
+    hf_veff = rng.standard_normal((p.nao, p.nao))
+    hf_veff = hf_veff + hf_veff.T
+    rdms = [d[1] for d in dms.values()]
+    out = consumer.initialize_fragments(b, p.TAs, p.MO_coeff_epsilon, hf_dm, S, hf_veff, rdms, n_frags=[3] * len(p.TAs))
+    for i, TA in enumerate(p.TAs):
+        G = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+        veff_w, veff0_w = co.get_veff(G, hf_dm, S, TA, hf_veff)
+        e2_w = co.ebe_hf_two_electron(G, rdms[i], 3)
+        assert np.abs(out[i]["veff"] - veff_w).max() <= 1e-9 * max(1.0, float(np.abs(veff_w).max()))
+        assert np.abs(out[i]["veff0"] - veff0_w).max() <= 1e-12 * max(1.0, float(np.abs(veff0_w).max()))
+        assert np.abs(out[i]["e2"] - e2_w).max() <= 1e-9 * max(1.0, float(np.abs(e2_w).max()))
+    b.close()

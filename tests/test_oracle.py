@@ -134,6 +134,43 @@ def test_consumer_oracle_identity():
     assert np.abs(e2 - np.einsum("ij,ij->i", D[:n_frag], 2 * vj[:n_frag] - vk[:n_frag])).max() <= 1e-12
 
 
+def test_consumer_oracle_two_independent_restatements_of_dot_eri_dm():
+    """dot_eri_dm (PySCF, absent everywhere): the einsum restatement of its 4-index branch against explicit
+    restore(1)-by-definition loops, on reference-produced (ij|kl) matrices, symmetric and non-symmetric dm."""
+    from oracle import consumer_oracle as co
+
+    rng = np.random.default_rng(11)
+    for name, f in (("chain_small", 0), ("lattice_small", 1)):
+        g = Golden(name)
+        fr = g.frag(f)
+        nmo_full = fr["TA"].shape[1]
+        nmo = min(nmo_full, 10)
+        # leading nmo x nmo block of orbitals: its pairs are the first nmo(nmo+1)/2 pair indices (T(max)+min order)
+        npair = nmo * (nmo + 1) // 2
+        G = np.ascontiguousarray(fr["G"][:npair, :npair])
+        for sym in (True, False):
+            dm = rng.standard_normal((nmo, nmo))
+            if sym:
+                dm = dm + dm.T
+            vj, vk = co.dot_eri_dm(G, dm)
+            wj, wk = co.dot_eri_dm_loops(G, dm)
+            assert np.abs(vj - wj).max() <= 1e-12 * max(1.0, np.abs(wj).max())
+            assert np.abs(vk - wk).max() <= 1e-12 * max(1.0, np.abs(wk).max())
+        # restore(1) by loops == fancy-index unpacking, and carries the 8-fold symmetry of real ERIs
+        e1, e2 = co.restore1_loops(G, nmo), co.unpack_s4(G, nmo)
+        assert np.array_equal(e1, e2)
+        assert np.array_equal(e1, e1.transpose(1, 0, 2, 3)) and np.array_equal(e1, e1.transpose(0, 1, 3, 2))
+        assert np.abs(e1 - e1.transpose(2, 3, 0, 1)).max() <= 1e-14 * np.abs(e1).max()
+        # J/K energy identities that need no unpacking convention: E_J = D:vj(D) = sum_{pq} Dp_p G_pq Dp_q with the
+        # packed density (off-diagonals doubled)
+        D = rng.standard_normal((nmo, nmo))
+        D = D + D.T
+        vj, vk = co.dot_eri_dm(G, D)
+        tri = np.tril_indices(nmo)
+        Dp = np.where(tri[0] == tri[1], 1.0, 2.0) * D[tri]
+        assert abs(np.sum(D * vj) - Dp @ G @ Dp) <= 1e-11 * max(1.0, abs(Dp @ G @ Dp))
+
+
 def _int8_test_operand(rng, naux=300, npair=90):
     X = rng.standard_normal((naux, npair)) * np.exp(-6 * rng.random(npair))[None, :] * np.exp(-4 * rng.random(naux))[:, None]
     X[:, 7] = 0.0                                   # an all-zero pair
