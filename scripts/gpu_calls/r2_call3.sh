@@ -14,3 +14,6 @@ for tool in memcheck synccheck racecheck; do
 done
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-file gpurun_out/r2c3_launches.csv \
   python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-file --e2e-steps 1 > gpurun_out/r2c3_ncu_bench.log 2>&1; echo "ncu launches exit $?"
+timeout 300 python scripts/ref_cuda_bar.py cuda > gpurun_out/r2c3_refbar_shipped.log 2>&1; echo "ref bar shipped exit $?"; tail -n 3 gpurun_out/r2c3_refbar_shipped.log
+timeout 300 python scripts/ref_cuda_bar.py cuda_betafix > gpurun_out/r2c3_refbar_betafix.log 2>&1; echo "ref bar betafix exit $?"; tail -n 3 gpurun_out/r2c3_refbar_betafix.log
+timeout 600 python scripts/sweep.py --low --out gpurun_out/r2c3_sweep_low.json > gpurun_out/r2c3_sweep_low.log 2>&1; echo "sweep low exit $?"; tail -n 8 gpurun_out/r2c3_sweep_low.log | cut -c1-700

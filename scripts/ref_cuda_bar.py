@@ -1,8 +1,10 @@
 """The reference's OWN GPU variant as a bar (SURVEY 8d / acceptance 6): `transform_integral_cuda` of the unmodified
 extension built with -DUSE_CUDA (oracle/_ref/cuda: CPU K1/K2a, then cublasDtrsm + cublasDsyrk with per-call
 cudaMalloc, synchronous H2D/D2H and a serial host mirror, cpp:624-736) next to this repository's path on the same
-fragments, same host buffers in and out.  The reference variant adds its result to uninitialised memory
-(beta = 1), so only its TIME is meaningful; its output is not compared."""
+fragments, same host buffers in and out.  Two builds of the reference are timed: "as shipped" (oracle/_ref/cuda: its
+dsyrk adds to uninitialised memory, beta = 1, SURVEY F4 -- only its TIME is meaningful) and "beta fixed"
+(oracle/_ref/cuda_betafix: the same sources with beta = 0, patched into a scratch copy by oracle/patch_beta.py), whose
+OUTPUT is also compared with this repository's (ij|kl)."""
 import importlib.util
 import json
 import sys
@@ -16,9 +18,10 @@ import numpy as np
 from quemb_b200 import eri_sparse_DF as q
 from quemb_b200 import synthetic as syn
 
-so = next((ROOT / "oracle" / "_ref" / "cuda").glob("eri_sparse_DF*.so"), None)
+variant = sys.argv[1] if len(sys.argv) > 1 else "cuda"  # "cuda" (as shipped) or "cuda_betafix"
+so = next((ROOT / "oracle" / "_ref" / variant).glob("eri_sparse_DF*.so"), None)
 if so is None:
-    raise SystemExit("oracle/_ref/cuda not built")
+    raise SystemExit(f"oracle/_ref/{variant} not built")
 spec = importlib.util.spec_from_file_location("eri_sparse_DF", str(so))
 ref = importlib.util.module_from_spec(spec)
 spec.loader.exec_module(ref)
@@ -40,7 +43,6 @@ for f in (0, 2):
         t0 = time.perf_counter()
         G_ref = ref.transform_integral_cuda(T_ref, TA, p.S_abs, L_ref, p.MO_coeff_epsilon)
         t_ref.append(time.perf_counter() - t0)
-    del G_ref
     t_b = []
     for _ in range(3):
         t0 = time.perf_counter()
@@ -51,7 +53,10 @@ for f in (0, 2):
         t0 = time.perf_counter()
         G = q.transform_integral(Tw, TA, p.S_abs, None, p.MO_coeff_epsilon)
         t_w.append(time.perf_counter() - t0)
-    row = {"fragment": f, "nmo": nmo, "npair": npair, "G_gb": npair * npair * 8 / 1e9,
+    parity = float(np.abs(G - G_ref).max()) if variant == "cuda_betafix" else None
+    del G_ref
+    row = {"fragment": f, "nmo": nmo, "npair": npair, "G_gb": npair * npair * 8 / 1e9, "reference_variant": variant,
+           "max_abs_b200_vs_reference_gpu_variant": parity,
            "reference_transform_integral_cuda_s": min(t_ref),
            "b200_transform_integral_s": min(t_b), "b200_whitened_s": min(t_w),
            "speedup_vs_reference_gpu_variant": min(t_ref) / min(t_w),
@@ -59,4 +64,4 @@ for f in (0, 2):
     print(json.dumps(row), flush=True)
     out.append(row)
 Path("gpurun_out").mkdir(exist_ok=True)
-Path("gpurun_out/ref_cuda_bar.json").write_text(json.dumps(out, indent=1))
+Path(f"gpurun_out/ref_cuda_bar_{variant}.json").write_text(json.dumps(out, indent=1))

@@ -54,12 +54,15 @@ def make_point(nmo: int, naux: int, max_bytes: float):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--low", action="store_true", help="only the low end: nmo {20, 50, 100} x naux {500, 2000}")
     ap.add_argument("--out", default="gpurun_out/sweep.json")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--max-gb", type=float, default=3.0)
     args = ap.parse_args()
     nmos = [20, 100, 400] if args.quick else [20, 50, 100, 150, 200, 300, 400]
     nauxs = [500, 8000] if args.quick else [500, 1000, 2000, 4000, 8000]
+    if args.low:
+        nmos, nauxs = [20, 50, 100], [500, 2000]
     peak = dgemm_peak()
     ctx = q.default_context(0)
     ctx.set_timing(True)
