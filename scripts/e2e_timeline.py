@@ -1,6 +1,6 @@
 """Where the wall time of one end-to-end build goes, per rank (host view), at N = 1 / 2 / 4 / 8.
 
-  python scripts/e2e_timeline.py [--output triangle|full] [--upload replicated|sharded] [--reps 3]
+  python scripts/e2e_timeline.py [--modes triangle:replicated,triangle:sharded,full:sharded] [--reps 3]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 scripts/e2e_timeline.py ...
 
 Per rank and repetition: upload (host -> device of (P|mu nu)), stage (L, S_abs, metric application incl. the NCCL
@@ -26,8 +26,8 @@ from quemb_b200.driver import FragmentERIBuilder, fragment_cost, partition_lpt
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--output", default="triangle", choices=["triangle", "full"])
-    ap.add_argument("--upload", default="sharded", choices=["replicated", "sharded"])
+    ap.add_argument("--modes", default="triangle:sharded,full:sharded",
+                    help="comma list of <output>:<upload>; output = triangle | full, upload = replicated | sharded")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--buffers", type=int, default=3)
     ap.add_argument("--out", default="gpurun_out/e2e_timeline.jsonl")
@@ -53,7 +53,6 @@ def main():
     mine = partition_lpt(costs, world)[rank]
     b = FragmentERIBuilder(local, n_host_buffers=args.buffers)
     ctx = b.ctx
-    ctx.set_output_mode(args.output == "triangle")
     T = q.SemiSparseSym3DTensor((p.naux, p.nao, p.nao), p.exch_reachable, ctx=ctx)
     b.reserve_host(max(t.shape[1] for t in p.TAs))
     hw, hc = q.host_bandwidth(1 << 30)
@@ -78,60 +77,63 @@ def main():
         chk.append(float(G[0, 0]) + float(G[-1, 0]) + float(G[0, -1]))
         log["sink_s"] = log.get("sink_s", 0.0) + time.perf_counter() - t
 
-    rows = []
-    for rep in range(args.reps + 1):
-        log.clear()
-        barrier()
-        x0 = ctx.transfer_bytes
-        t0 = time.perf_counter()
-        if world == 1 or args.upload == "replicated":
-            T.upload(p.unique_dense_data)
-            ctx.synchronize()
-            t1 = time.perf_counter()
-            b.stage(None, None, None, p.L_PQ, p.S_abs, whiten=False, tensor=T)
-            if dist is None:
-                T.whiten(b.metric)
+    for mode in args.modes.split(","):
+        output, upload = mode.split(":")
+        ctx.set_output_mode(output == "triangle")
+        rows = []
+        for rep in range(args.reps + 1):
+            log.clear()
+            barrier()
+            x0 = ctx.transfer_bytes
+            t0 = time.perf_counter()
+            if world == 1 or upload == "replicated":
+                T.upload(p.unique_dense_data)
+                ctx.synchronize()
+                t1 = time.perf_counter()
+                b.stage(None, None, None, p.L_PQ, p.S_abs, whiten=False, tensor=T)
+                if dist is None:
+                    T.whiten(b.metric)
+                else:
+                    T.whiten_distributed(b.metric, dist)
             else:
-                T.whiten_distributed(b.metric, dist)
-        else:
-            t1 = t0
-            b.stage_distributed(p.unique_dense_data, p.L_PQ, p.S_abs, dist, tensor=T)
-        ctx.synchronize()
-        t2 = time.perf_counter()
-        b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
-        ctx.synchronize()
-        t3 = time.perf_counter()
-        barrier()
-        t4 = time.perf_counter()
-        x1 = ctx.transfer_bytes
-        if rep == 0:
-            continue  # warm-up
-        res = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in mine)
-        rows.append({"rep": rep, "upload_s": t1 - t0, "stage_s": t2 - t1, "build_s": t3 - t2, "total_s": t3 - t0,
-                     "all_ranks_done_s": t4 - t0, **{k: v for k, v in log.items()},
-                     "h2d_gb": (x1[0] - x0[0]) / 1e9, "d2h_gb": (x1[1] - x0[1]) / 1e9, "result_gb": res / 1e9,
-                     "delivery_gbs": res / (t3 - t2) / 1e9})
-    mean = {k: float(np.mean([r[k] for r in rows])) for k in rows[0] if k != "rep"}
-    mine_rec = {"rank": rank, "fragments": len(mine), "host_threads": bench.q_host_threads(_lib),
-                "host_write_gbs_rank_threads": hw, "host_copy_gbs_rank_threads": hc, "mean": mean, "reps": rows}
-    allrec = [mine_rec]
-    if dist is not None:
-        allrec = [None] * world
-        dist.all_gather_object(allrec, mine_rec)
-    if rank == 0:
-        line = {"n_gpus": world, "output": args.output, "upload": args.upload, "buffers": args.buffers,
-                "cores": len(os.sched_getaffinity(0)),
-                "e2e_s_max_over_ranks": max(r["mean"]["total_s"] for r in allrec),
-                "all_ranks_done_s": max(r["mean"]["all_ranks_done_s"] for r in allrec),
-                "result_gb_total": sum(r["mean"]["result_gb"] for r in allrec),
-                "ranks": allrec}
-        line["aggregate_delivery_gbs"] = line["result_gb_total"] / line["e2e_s_max_over_ranks"]
-        Path(args.out).parent.mkdir(parents=True, exist_ok=True)
-        with open(args.out, "a") as f:
-            f.write(json.dumps(line) + "\n")
-        brief = {k: v for k, v in line.items() if k != "ranks"}
-        brief["rank0_mean"] = allrec[0]["mean"]
-        print(json.dumps(brief), flush=True)
+                t1 = t0
+                b.stage_distributed(p.unique_dense_data, p.L_PQ, p.S_abs, dist, tensor=T)
+            ctx.synchronize()
+            t2 = time.perf_counter()
+            b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
+            ctx.synchronize()
+            t3 = time.perf_counter()
+            barrier()
+            t4 = time.perf_counter()
+            x1 = ctx.transfer_bytes
+            if rep == 0:
+                continue  # warm-up
+            res = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in mine)
+            rows.append({"rep": rep, "upload_s": t1 - t0, "stage_s": t2 - t1, "build_s": t3 - t2, "total_s": t3 - t0,
+                         "all_ranks_done_s": t4 - t0, **{k: v for k, v in log.items()},
+                         "h2d_gb": (x1[0] - x0[0]) / 1e9, "d2h_gb": (x1[1] - x0[1]) / 1e9, "result_gb": res / 1e9,
+                         "delivery_gbs": res / (t3 - t2) / 1e9})
+        mean = {k: float(np.mean([r[k] for r in rows])) for k in rows[0] if k != "rep"}
+        mine_rec = {"rank": rank, "fragments": len(mine), "host_threads": bench.q_host_threads(_lib),
+                    "host_write_gbs_rank_threads": hw, "host_copy_gbs_rank_threads": hc, "mean": mean, "reps": rows}
+        allrec = [mine_rec]
+        if dist is not None:
+            allrec = [None] * world
+            dist.all_gather_object(allrec, mine_rec)
+        if rank == 0:
+            line = {"n_gpus": world, "output": output, "upload": upload, "buffers": args.buffers,
+                    "cores": len(os.sched_getaffinity(0)),
+                    "e2e_s_max_over_ranks": max(r["mean"]["total_s"] for r in allrec),
+                    "all_ranks_done_s": max(r["mean"]["all_ranks_done_s"] for r in allrec),
+                    "result_gb_total": sum(r["mean"]["result_gb"] for r in allrec),
+                    "ranks": allrec}
+            line["aggregate_delivery_gbs"] = line["result_gb_total"] / line["e2e_s_max_over_ranks"]
+            Path(args.out).parent.mkdir(parents=True, exist_ok=True)
+            with open(args.out, "a") as f:
+                f.write(json.dumps(line) + "\n")
+            brief = {k: v for k, v in line.items() if k != "ranks"}
+            brief["rank0_mean"] = allrec[0]["mean"]
+            print(json.dumps(brief), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
