@@ -2,10 +2,15 @@
 // include/qemb_b200.h.  Reference citations: "cpp:" = src/quemb/molbe/_cpp/eri_sparse_DF.cpp,
 // "hpp:" = src/quemb/molbe/_cpp/indexers.hpp of troyvvgroup/quemb.
 //
-// Streams per context:
-//   compute  K1, K2a, K2b, K3 of consecutive fragments, in order
-//   prep     TA upload, screening kernel, mask download, plan upload of the NEXT fragment
-//   copy     device -> host copy of a finished G while the next fragment computes
+// Streams:
+//   ctx compute  tensor / metric level work (uploads, block staging, metric application), in order
+//   ctx copy     device -> host copy of a finished G while the next fragment computes
+//   ws compute   K1, K2a, K2b, K3 (and the J/K consumer) of the fragments of ONE workspace, in order
+//   ws prep      TA upload, screening kernel, plan upload of that workspace's NEXT fragment
+// Every workspace owns its two streams, so concurrent callers (one workspace each; the reference's
+// ThreadPoolExecutor(n_threads), eri_sparse_DF.py:649-653) overlap on the device and fragments too small to fill
+// 148 SMs share them.  A fragment forks from the ctx compute stream (it sees every tensor update enqueued before
+// it); tensor updates, marks and stream hand-offs join the workspace streams first (fork_from_ctx / join_workspaces).
 // Fragment-local inputs (TA, mask, plan tables) are double buffered ("slots"), and so is G when it has
 // to travel to the host, so that back-to-back qemb_fragment_transform calls pipeline without any
 // host-side wait on the compute stream.
@@ -94,7 +99,7 @@ struct qemb_ctx {
     int device = 0;
     cudaStream_t compute = nullptr, prep = nullptr, copy = nullptr;
     bool timing = false;
-    int64_t launches = 0;
+    std::atomic<int64_t> launches{0};
     cudaEvent_t marks[16] = {};
     // how a host-bound G travels: 1 = lower triangle over PCIe + mirror on the host cores (default),
     // 0 = the full square over PCIe
@@ -105,7 +110,12 @@ struct qemb_ctx {
     // 0: K3 on the FP64 tensor path (default, the parity reference); 5 .. 8: opt-in int8-slice K3 (k3_int8.cu)
     int k3_slices = 0;
     int num_sms = 148;
-    int64_t h2d_bytes = 0, d2h_bytes = 0; // bytes handed to the copy engines (uploads / G transfers)
+    std::atomic<int64_t> h2d_bytes{0}, d2h_bytes{0}; // bytes handed to the copy engines (uploads / G transfers)
+    // every workspace runs its fragments on streams of its own (concurrent callers overlap on the device, small
+    // fragments that do not fill 148 SMs share them); operations on the context's compute stream that must see or
+    // must not overtake fragment work join these streams first (join_workspaces)
+    std::mutex ws_mutex;
+    std::vector<qemb_workspace *> workspaces;
     // host-bound G transfers whose host mirror has not finished yet (qemb_ctx_synchronize waits for them)
     std::mutex out_mutex;
     std::condition_variable out_cv;
@@ -333,6 +343,8 @@ inline void wait_job(OutJob &job)
 
 struct qemb_workspace {
     qemb_ctx *ctx = nullptr;
+    cudaStream_t compute = nullptr, prep = nullptr; // this workspace's own streams
+    cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
     Slot slot[2];
     int cur = 0;
     bool started = false;
@@ -372,6 +384,41 @@ struct qemb_workspace {
     bool ev_valid[5] = {false, false, false, false, false};
     bool evs_valid = false;
 };
+
+namespace {
+
+// the workspace's streams continue behind everything enqueued on the context's compute stream so far (tensor
+// uploads, metric application, collectives handed over with qemb_ctx_stream_handoff)
+int fork_from_ctx(qemb_workspace *w)
+{
+    CU(cudaEventRecord(w->fork_ev, w->ctx->compute));
+    CU(cudaStreamWaitEvent(w->compute, w->fork_ev, 0));
+    CU(cudaStreamWaitEvent(w->prep, w->fork_ev, 0));
+    return QEMB_OK;
+}
+
+// the context's compute stream continues behind the fragment work of every workspace enqueued so far
+int join_workspaces(qemb_ctx *c)
+{
+    std::lock_guard<std::mutex> lk(c->ws_mutex);
+    for (qemb_workspace *w : c->workspaces) {
+        CU(cudaEventRecord(w->join_ev, w->compute));
+        CU(cudaStreamWaitEvent(c->compute, w->join_ev, 0));
+    }
+    return QEMB_OK;
+}
+
+int sync_workspaces(qemb_ctx *c)
+{
+    std::lock_guard<std::mutex> lk(c->ws_mutex);
+    for (qemb_workspace *w : c->workspaces) {
+        CU(cudaStreamSynchronize(w->prep));
+        CU(cudaStreamSynchronize(w->compute));
+    }
+    return QEMB_OK;
+}
+
+} // namespace
 
 // ------------------------------------------------------------------------------------------------
 // device / ctx
@@ -443,6 +490,7 @@ extern "C" int qemb_ctx_synchronize(qemb_ctx *c)
 {
     REQ(c != nullptr, "null ctx");
     DeviceGuard g(c->device);
+    TRY(sync_workspaces(c));
     CU(cudaStreamSynchronize(c->prep));
     CU(cudaStreamSynchronize(c->compute));
     CU(cudaStreamSynchronize(c->copy));
@@ -526,6 +574,7 @@ extern "C" int qemb_ctx_mark(qemb_ctx *c, int id, int stream)
     REQ(c != nullptr && id >= 0 && id < 16 && stream >= 0 && stream < 3, "bad argument");
     DeviceGuard g(c->device);
     if (!c->marks[id]) CU(cudaEventCreate(&c->marks[id]));
+    if (stream == 0) TRY(join_workspaces(c)); // a mark on the compute stream brackets the fragment work as well
     CU(cudaEventRecord(c->marks[id], stream == 0 ? c->compute : stream == 1 ? c->prep : c->copy));
     return QEMB_OK;
 }
@@ -608,6 +657,7 @@ extern "C" int qemb_ctx_stream_handoff(qemb_ctx *c, void *external_stream, int d
     REQ(c && (direction == 0 || direction == 1), "bad argument");
     DeviceGuard g(c->device);
     cudaStream_t ext = static_cast<cudaStream_t>(external_stream);
+    if (direction == 0) TRY(join_workspaces(c));
     cudaEvent_t e;
     CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     cudaError_t rc = cudaEventRecord(e, direction == 0 ? c->compute : ext);
@@ -745,6 +795,7 @@ extern "C" void qemb_tensor_destroy(qemb_tensor *t)
 {
     if (!t) return;
     DeviceGuard g(t->ctx->device);
+    sync_workspaces(t->ctx);
     cudaStreamSynchronize(t->ctx->compute);
     t->data.release();
     t->d_rcol.release();
@@ -804,6 +855,7 @@ extern "C" int qemb_tensor_upload(qemb_tensor *t, const double *host, int64_t ld
         "partial upload into a whitened tensor (call qemb_tensor_set_whitened(t, 0) first)");
     DeviceGuard g(t->ctx->device);
     NvtxRange nv("qemb:tensor_upload");
+    TRY(join_workspaces(t->ctx)); // fragments still reading the old content finish first
     cudaStream_t s = t->ctx->compute;
     TRY(upload_2d(t->ctx, t->data.as<double>() + col0 * t->ldp, (size_t)t->ldp * 8, host, (size_t)ld_host * 8,
                   (size_t)t->naux * 8, (size_t)ncols, s));
@@ -839,6 +891,7 @@ extern "C" int qemb_tensor_scatter_block(qemb_tensor *t, const double *block, in
     REQ(!t->whitened, "block staging into a whitened tensor (call qemb_tensor_set_whitened(t, 0) first)");
     DeviceGuard g(t->ctx->device);
     NvtxRange nv("qemb:scatter_block");
+    TRY(join_workspaces(t->ctx));
     cudaStream_t s = t->ctx->compute;
     const size_t bbytes = (size_t)npairs * (size_t)t->naux * 8, cbytes = (size_t)npairs * 4;
     const size_t coff = (bbytes + 15) & ~size_t(15);
@@ -938,6 +991,7 @@ extern "C" void qemb_metric_destroy(qemb_metric *m)
 {
     if (!m) return;
     DeviceGuard g(m->ctx->device);
+    sync_workspaces(m->ctx);
     cudaStreamSynchronize(m->ctx->compute);
     m->L.release();
     m->Dinv.release();
@@ -951,6 +1005,8 @@ extern "C" int qemb_tensor_whiten(qemb_tensor *t, const qemb_metric *m)
     REQ(t->naux == m->naux, "naux mismatch between tensor and metric");
     REQ(!t->whitened, "tensor is already whitened");
     DeviceGuard g(t->ctx->device);
+    NvtxRange nv("qemb:tensor_whiten");
+    TRY(join_workspaces(t->ctx));
     TrsmParams p;
     p.L = m->L.as<double>();
     p.ldl = m->naux_pad;
@@ -981,6 +1037,7 @@ extern "C" int qemb_tensor_upload_whitened_rows(qemb_tensor *t, const qemb_metri
     if (ncols == 0) return QEMB_OK;
     DeviceGuard g(t->ctx->device);
     qemb_ctx *c = t->ctx;
+    TRY(join_workspaces(c));
     cudaStream_t s = c->compute;
     const int64_t p_end = p_begin + t->naux;
     const int64_t mrows = round_up(p_end, 16);
@@ -1028,6 +1085,7 @@ extern "C" int qemb_tensor_whiten_range(qemb_tensor *t, const qemb_metric *m, in
     REQ(col0 >= 0 && ncols >= 0 && col0 + ncols <= t->n_unique, "column range outside the tensor");
     if (ncols == 0) return QEMB_OK;
     DeviceGuard g(t->ctx->device);
+    TRY(join_workspaces(t->ctx));
     TrsmParams p;
     p.L = m->L.as<double>();
     p.ldl = m->naux_pad;
@@ -1064,6 +1122,7 @@ extern "C" int qemb_tensor_copy_data(qemb_tensor *dst, const qemb_tensor *src)
     REQ(dst->naux == src->naux && dst->nao == src->nao && dst->n_unique == src->n_unique && dst->rcol == src->rcol,
         "tensors have different shapes or lists");
     DeviceGuard g(dst->ctx->device);
+    TRY(join_workspaces(dst->ctx));
     CU(cudaMemcpyAsync(dst->data.p, src->data.p, (size_t)src->ldp * (size_t)src->n_unique * 8, cudaMemcpyDeviceToDevice,
                        dst->ctx->compute));
     dst->whitened = src->whitened;
@@ -1106,6 +1165,7 @@ extern "C" void qemb_screen_destroy(qemb_screen *s)
 {
     if (!s) return;
     DeviceGuard g(s->ctx->device);
+    sync_workspaces(s->ctx);
     s->S.release();
     delete s;
 }
@@ -1121,6 +1181,14 @@ extern "C" int qemb_workspace_create(qemb_ctx *ctx, qemb_workspace **out)
     qemb_workspace *w = new (std::nothrow) qemb_workspace;
     if (!w) return fail(QEMB_ENOMEM, "host allocation failed");
     w->ctx = ctx;
+    CU(cudaStreamCreateWithFlags(&w->compute, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&w->prep, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&w->fork_ev, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&w->join_ev, cudaEventDisableTiming));
+    {
+        std::lock_guard<std::mutex> lk(ctx->ws_mutex);
+        ctx->workspaces.push_back(w);
+    }
     for (int i = 0; i < 2; ++i) {
         CU(cudaEventCreateWithFlags(&w->slot[i].uploaded1, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&w->slot[i].uploaded2, cudaEventDisableTiming));
@@ -1142,6 +1210,15 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     DeviceGuard g(w->ctx->device);
     qemb_ctx_synchronize(w->ctx);
     for (int i = 0; i < OUT_RING; ++i) wait_job(w->jobs[i]);
+    {
+        std::lock_guard<std::mutex> lk(w->ctx->ws_mutex);
+        auto &v = w->ctx->workspaces;
+        v.erase(std::remove(v.begin(), v.end(), w), v.end());
+    }
+    cudaStreamDestroy(w->compute);
+    cudaStreamDestroy(w->prep);
+    cudaEventDestroy(w->fork_ev);
+    cudaEventDestroy(w->join_ev);
     for (int i = 0; i < 2; ++i) {
         Slot &s = w->slot[i];
         s.TA.release();
@@ -1198,6 +1275,7 @@ namespace {
 // with its TA / plan tables
 int begin_fragment(qemb_workspace *w, int64_t nao, int64_t nmo)
 {
+    TRY(fork_from_ctx(w));
     if (w->started) w->cur ^= 1;
     w->started = true;
     Slot &s = w->slot[w->cur];
@@ -1221,9 +1299,9 @@ int upload_TA(qemb_workspace *w, const double *TA, int64_t ld)
     Slot &s = w->slot[w->cur];
     TRY(s.TA.reserve((size_t)s.nao * s.nmo * 8));
     CU(cudaMemcpy2DAsync(s.TA.p, (size_t)s.nao * 8, TA, (size_t)ld * 8, (size_t)s.nao * 8, (size_t)s.nmo,
-                         cudaMemcpyHostToDevice, w->ctx->prep));
+                         cudaMemcpyHostToDevice, w->prep));
     w->ctx->h2d_bytes += s.nao * s.nmo * 8;
-    CU(cudaEventRecord(s.ta_ready, w->ctx->prep));
+    CU(cudaEventRecord(s.ta_ready, w->prep));
     return QEMB_OK;
 }
 
@@ -1309,8 +1387,8 @@ int build_plan2(qemb_workspace *w)
     s.work[1] = f2 * (double)w->naux;                               // F_K2a
     s.work[5] = 8.0 * (double)w->naux * ((double)nA + (double)npair); // Bytes_K2a
     w->ctx->h2d_bytes += (int64_t)total;
-    CU(cudaMemcpyAsync(s.plan2.p, h, total, cudaMemcpyHostToDevice, w->ctx->prep));
-    CU(cudaEventRecord(s.uploaded2, w->ctx->prep));
+    CU(cudaMemcpyAsync(s.plan2.p, h, total, cudaMemcpyHostToDevice, w->prep));
+    CU(cudaEventRecord(s.uploaded2, w->prep));
     char *d = static_cast<char *>(s.plan2.p);
     s.pd.acol2 = (const int *)(d + o_acol);
     s.pd.brow2 = (const int *)(d + o_brow);
@@ -1389,8 +1467,8 @@ int build_plan1(qemb_workspace *w, const qemb_tensor *t)
     s.work[0] = f1 * (double)w->naux;                                                          // F_K1
     s.work[4] = 8.0 * (double)w->naux * ((double)U + (double)nA) + 8.0 * (double)nao * (double)nmo; // Bytes_K1
     w->ctx->h2d_bytes += (int64_t)total;
-    CU(cudaMemcpyAsync(s.plan1.p, h, total, cudaMemcpyHostToDevice, w->ctx->prep));
-    CU(cudaEventRecord(s.uploaded1, w->ctx->prep));
+    CU(cudaMemcpyAsync(s.plan1.p, h, total, cudaMemcpyHostToDevice, w->prep));
+    CU(cudaEventRecord(s.uploaded1, w->prep));
     char *d = static_cast<char *>(s.plan1.p);
     s.pd.bcol1 = (const int *)(d + o_bcol);
     s.pd.ccol1 = (const int *)(d + o_ccol);
@@ -1427,8 +1505,8 @@ int get_gram_tiles(qemb_workspace *w, int nt, const int2 **tiles, int *count)
         DevBuf b;
         TRY(b.reserve(std::max<size_t>(h.size(), 1) * sizeof(int2)));
         // blocking copy on the prep stream: happens once per distinct tile count
-        CU(cudaMemcpyAsync(b.p, h.data(), h.size() * sizeof(int2), cudaMemcpyHostToDevice, w->ctx->prep));
-        CU(cudaStreamSynchronize(w->ctx->prep));
+        CU(cudaMemcpyAsync(b.p, h.data(), h.size() * sizeof(int2), cudaMemcpyHostToDevice, w->prep));
+        CU(cudaStreamSynchronize(w->prep));
         it = w->gram_tiles.emplace(nt, std::make_pair(b, (int)n)).first;
     }
     *tiles = it->second.first.as<int2>();
@@ -1453,7 +1531,7 @@ extern "C" int qemb_fragment_screen(qemb_workspace *w, const qemb_screen *sc, co
     // device -> host memcpy here would queue behind the multi-GB G transfer of the previous fragment on the
     // D2H copy engine and stall the host (measured: 110-137 ms per fragment instead of 85)
     TRY(s.hmask.reserve((size_t)nao * nmo));
-    cudaStream_t ps = w->ctx->prep;
+    cudaStream_t ps = w->prep;
     if (w->ctx->timing) CU(cudaEventRecord(w->evs[0], ps));
     CU(launch_screen(sc->S.as<double>(), nao, s.TA.as<double>(), nao, (int)nao, (int)nmo, eps, static_cast<uint8_t *>(s.hmask.p), ps));
     w->ctx->launches += 1;
@@ -1528,7 +1606,7 @@ int contract_1st(qemb_workspace *w, const qemb_tensor *t, int64_t p0, int64_t p1
     w->mrows = round_up(p1, 16) - p0;
     TRY(build_plan1(w, t));
     TRY(w->Bint.reserve((size_t)w->ldp * (size_t)std::max<int64_t>(s.nA, 1) * 8));
-    cudaStream_t cs = w->ctx->compute;
+    cudaStream_t cs = w->compute;
     CU(cudaStreamWaitEvent(cs, s.ta_ready, 0));
     CU(cudaStreamWaitEvent(cs, s.uploaded1, 0));
     GatherParams p;
@@ -1569,7 +1647,7 @@ int contract_2nd(qemb_workspace *w)
     REQ(w->have_B, "contract_1st has not run for this fragment");
     TRY(build_plan2(w));
     TRY(w->sym.reserve((size_t)w->ldp * (size_t)s.npair * 8));
-    cudaStream_t cs = w->ctx->compute;
+    cudaStream_t cs = w->compute;
     CU(cudaStreamWaitEvent(cs, s.uploaded2, 0));
     GatherParams p;
     p.Asrc = w->Bint.as<double>();
@@ -1620,7 +1698,7 @@ int solve(qemb_workspace *w, const qemb_metric *m)
     p.X = w->sym.as<double>();
     p.ldx = w->ldp;
     p.ncol = s.npair;
-    cudaStream_t cs = w->ctx->compute;
+    cudaStream_t cs = w->compute;
     CU(launch_trsm_rows(p, (int)w->mrows, cs));
     w->ctx->launches += 1;
     if (w->ctx->timing) {
@@ -1653,7 +1731,7 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         TRY(w->gram_partial.reserve((size_t)nsplit * (size_t)s.npair * (size_t)s.npair * 8));
         p.partial = w->gram_partial.as<double>();
     }
-    cudaStream_t cs = w->ctx->compute;
+    cudaStream_t cs = w->compute;
     if (w->ctx->timing && !w->ev_valid[3]) { // no solve in between: K3 starts where K2a ended
         CU(cudaEventRecord(w->ev[3], cs));
         w->ev_valid[3] = true;
@@ -1698,7 +1776,7 @@ int gram_ws(qemb_workspace *w)
     const int gi = w->gi;
     TRY(w->G[gi].reserve((size_t)s.npair * (size_t)s.npair * 8));
     if (w->g_copy_pending[gi]) { // the copy stream may still be reading this buffer
-        CU(cudaStreamWaitEvent(w->ctx->compute, w->g_copied[gi], 0));
+        CU(cudaStreamWaitEvent(w->compute, w->g_copied[gi], 0));
         w->g_copy_pending[gi] = false;
     }
     return gram(w, w->G[gi].as<double>(), s.npair);
@@ -1748,7 +1826,7 @@ extern "C" int qemb_fragment_get_B(const qemb_workspace *w, double *host, int64_
     REQ(ld >= w->naux, "ld < naux");
     if (s.nA == 0) return QEMB_OK;
     DeviceGuard g(w->ctx->device);
-    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaStreamSynchronize(w->compute));
     CU(cudaMemcpy2D(host, (size_t)ld * 8, w->Bint.p, (size_t)w->ldp * 8, (size_t)w->naux * 8, (size_t)s.nA,
                     cudaMemcpyDeviceToHost));
     return QEMB_OK;
@@ -1760,7 +1838,7 @@ extern "C" int qemb_fragment_get_sym(const qemb_workspace *w, double *host, int6
     const Slot &s = w->slot[w->cur];
     REQ(ld >= w->naux, "ld < naux");
     DeviceGuard g(w->ctx->device);
-    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaStreamSynchronize(w->compute));
     CU(cudaMemcpy2D(host, (size_t)ld * 8, w->sym.p, (size_t)w->ldp * 8, (size_t)w->naux * 8, (size_t)s.npair,
                     cudaMemcpyDeviceToHost));
     return QEMB_OK;
@@ -1772,7 +1850,7 @@ extern "C" int qemb_fragment_get_G(const qemb_workspace *w, double *host, int64_
     const Slot &s = w->slot[w->cur];
     REQ(ld >= s.npair, "ld < npair");
     DeviceGuard g(w->ctx->device);
-    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaStreamSynchronize(w->compute));
     CU(cudaMemcpy2D(host, (size_t)ld * 8, w->G_last, (size_t)w->G_last_ld * 8, (size_t)s.npair * 8, (size_t)s.npair,
                     cudaMemcpyDeviceToHost));
     return QEMB_OK;
@@ -1919,7 +1997,7 @@ static int transform_impl(qemb_workspace *w, const qemb_tensor *t, const qemb_me
     // hand G to the copy stream; the compute stream moves on to the next fragment
     cudaEvent_t done;
     CU(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
-    CU(cudaEventRecord(done, w->ctx->compute));
+    CU(cudaEventRecord(done, w->compute));
     CU(cudaStreamWaitEvent(w->ctx->copy, done, 0));
     CU(cudaEventDestroy(done));
     w->ticket += 1; // ticket k uses G buffer / event k & 1 (gi toggles once per host-output transform)
@@ -1979,7 +2057,7 @@ static int jk_impl(qemb_workspace *w, const double *D, int64_t ldd, double *vj, 
     REQ(amax <= 1e-12 * std::max(dmax, 1e-300) || amax == 0.0, "density matrix must be symmetric (hermi=1)");
     DeviceGuard g(w->ctx->device);
     NvtxRange nv("qemb:jk");
-    cudaStream_t cs = w->ctx->compute;
+    cudaStream_t cs = w->compute;
     // chunk table: whole packed rows, at most jk_chunk_doubles() doubles per chunk
     std::vector<int> crow{0};
     {
@@ -2134,6 +2212,7 @@ extern "C" int qemb_ipc_close(qemb_ctx *c, void *dev)
 {
     REQ(c && dev, "null argument");
     DeviceGuard g(c->device);
+    TRY(sync_workspaces(c));
     CU(cudaStreamSynchronize(c->compute));
     CU(cudaIpcCloseMemHandle(dev));
     return QEMB_OK;
@@ -2143,6 +2222,7 @@ extern "C" int qemb_ipc_free(qemb_ctx *c, void *dev)
 {
     REQ(c && dev, "null argument");
     DeviceGuard g(c->device);
+    TRY(sync_workspaces(c));
     CU(cudaStreamSynchronize(c->compute));
     CU(cudaFree(dev));
     return QEMB_OK;
@@ -2152,6 +2232,7 @@ extern "C" int qemb_device_zero(qemb_ctx *c, void *dev, int64_t bytes)
 {
     REQ(c && dev && bytes >= 0, "bad argument");
     DeviceGuard g(c->device);
+    TRY(join_workspaces(c));
     CU(cudaMemsetAsync(dev, 0, (size_t)bytes, c->compute));
     return QEMB_OK;
 }
@@ -2160,6 +2241,7 @@ extern "C" int qemb_device_mirror_lower(qemb_ctx *c, double *G, int64_t ld, int6
 {
     REQ(c && G && ld >= n && n >= 0, "bad argument");
     DeviceGuard g(c->device);
+    TRY(join_workspaces(c));
     CU(launch_mirror_lower(G, ld, n, c->compute));
     c->launches += 1;
     return QEMB_OK;
@@ -2169,6 +2251,7 @@ extern "C" int qemb_device_to_host(qemb_ctx *c, void *host, const void *dev, int
 {
     REQ(c && host && dev && bytes >= 0, "bad argument");
     DeviceGuard g(c->device);
+    TRY(join_workspaces(c));
     CU(cudaMemcpyAsync(host, dev, (size_t)bytes, cudaMemcpyDefault, c->compute)); // UVA: `host` may be any pointer
     c->d2h_bytes += bytes;
     CU(cudaStreamSynchronize(c->compute));
@@ -2203,8 +2286,8 @@ extern "C" int qemb_fragment_times(const qemb_workspace *w, float *ms5)
 {
     REQ(w && ms5, "null argument");
     DeviceGuard g(w->ctx->device);
-    CU(cudaStreamSynchronize(w->ctx->prep));
-    CU(cudaStreamSynchronize(w->ctx->compute));
+    CU(cudaStreamSynchronize(w->prep));
+    CU(cudaStreamSynchronize(w->compute));
     for (int i = 0; i < 5; ++i) ms5[i] = 0.f;
     if (w->evs_valid) CU(cudaEventElapsedTime(&ms5[0], w->evs[0], w->evs[1]));
     for (int i = 0; i < 4; ++i)

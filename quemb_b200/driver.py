@@ -57,16 +57,35 @@ def partition_lpt(costs: Sequence[float], n_parts: int) -> list[list[int]]:
     return [sorted(p) for p in parts]
 
 
+class _Lane:
+    """One caller's worth of per-fragment state: a workspace (own CUDA streams) + its pinned output ring."""
+
+    def __init__(self, ctx: q.Context, ws: q.Workspace | None = None):
+        self.ws = ws or q.Workspace(ctx)
+        self.bufs: list[np.ndarray] = []
+
+    def reserve(self, need: int, n: int) -> None:
+        if self.bufs and self.bufs[0].size >= need and len(self.bufs) == n:
+            return
+        self.free()
+        self.bufs = [_lib.pinned_empty((need,)) for _ in range(n)]
+
+    def free(self) -> None:
+        for b in self.bufs:
+            _lib.pinned_free(b)
+        self.bufs = []
+
+
 class FragmentERIBuilder:
     """Device-resident state of one molecule on ONE GPU + the pipelined per-fragment loop."""
 
     def __init__(self, device: int = 0, max_nmo: int | None = None, n_host_buffers: int = 3):
         self.ctx = q.default_context(device)
         self.ws = q.Workspace(self.ctx)
+        self._lanes: list[_Lane] = [_Lane(self.ctx, self.ws)]
         self.tensor: q.SemiSparseSym3DTensor | None = None
         self.metric: q.GPU_MatrixHandle | None = None
         self.screen = None
-        self._bufs: list[np.ndarray] = []
         # the library keeps completion state for `output_ring_depth()` pending host outputs per workspace; more
         # buffers than that would let a ticket be recycled before anybody waited for it
         depth = q.output_ring_depth()
@@ -107,46 +126,94 @@ class FragmentERIBuilder:
             tensor.upload(unique_dense_data[:, c0:c1], col0=c0)
         tensor.whiten_distributed(self.metric, dist, group=group)
 
-    def reserve_host(self, max_nmo: int) -> None:
+    @property
+    def _bufs(self) -> list[np.ndarray]:
+        return self._lanes[0].bufs
+
+    def reserve_host(self, max_nmo: int, lanes: int = 1) -> None:
         npair = max_nmo * (max_nmo + 1) // 2
-        need = npair * npair
-        if self._bufs and self._bufs[0].size >= need:
-            return
-        for b in self._bufs:
-            _lib.pinned_free(b)
-        self._bufs = [_lib.pinned_empty((need,)) for _ in range(self._n_host_buffers)]
+        while len(self._lanes) < lanes:
+            self._lanes.append(_Lane(self.ctx))
+        for lane in self._lanes[:lanes]:
+            lane.reserve(npair * npair, self._n_host_buffers)
 
     def close(self) -> None:
         self.ctx.synchronize()
-        for b in self._bufs:
-            _lib.pinned_free(b)
-        self._bufs = []
+        for lane in self._lanes:
+            lane.free()
 
     # -- the loop -------------------------------------------------------------------------------------
     def build(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, sink: Sink | None = None,
-              indices: Sequence[int] | None = None) -> None:
+              indices: Sequence[int] | None = None, n_threads: int = 1) -> None:
         """Transform the fragments ``indices`` (default: all) and hand every G to ``sink(i, G)``.
         ``G`` is a view of a pinned staging buffer, valid during the sink call -- or, when the sink returns a
         ``concurrent.futures.Future`` (e.g. :class:`quemb_b200.eri_file.AsyncDatasetWriter`), until that future
-        is done: the buffer is not handed to the device again before."""
+        is done: the buffer is not handed to the device again before.
+
+        ``n_threads > 1`` is the reference's ``ThreadPoolExecutor(n_threads)`` around its per-fragment worker
+        (``eri_sparse_DF.py:649-653``): that many host threads, each with a workspace (= CUDA streams) and an output
+        ring of its own, take fragments from a shared queue; the library calls release the GIL, the kernels of
+        different lanes overlap on the device -- what keeps 148 SMs busy when single fragments are too small to
+        (nmo <~ 100).  ``sink`` calls are serialised."""
         assert self.tensor is not None, "stage() first"
         idx = list(range(len(TAs))) if indices is None else list(indices)
         if not idx:
             return
-        self.reserve_host(max(TAs[i].shape[1] for i in idx))
-        nb = len(self._bufs)
+        n_threads = max(1, min(int(n_threads), len(idx)))
+        self._build_from(iter(idx), max(TAs[i].shape[1] for i in idx), TAs, MO_coeff_epsilon, sink, n_threads)
+
+    def _build_from(self, it, max_nmo: int, TAs, MO_coeff_epsilon: float, sink: Sink | None, n_threads: int = 1) -> None:
+        """The fragment loop over an ITERATOR of fragment indices (possibly shared with other devices' builders and
+        then already thread-safe): every lane keeps its own pipeline full until the iterator is exhausted."""
+        self.reserve_host(max_nmo, lanes=n_threads)
+        if n_threads == 1:
+            self._build_lane(self._lanes[0], it, TAs, MO_coeff_epsilon, sink)
+            return
+        it_lock, sink_lock = threading.Lock(), threading.Lock()
+
+        class Shared:
+            def __iter__(self):
+                return self
+
+            def __next__(self):
+                with it_lock:
+                    return next(it)
+
+        def locked_sink(i, G):
+            with sink_lock:
+                return sink(i, G)
+
+        errors: list[BaseException] = []
+
+        def run(lane):
+            try:
+                self._build_lane(lane, Shared(), TAs, MO_coeff_epsilon, None if sink is None else locked_sink)
+            except BaseException as e:  # noqa: BLE001
+                errors.append(e)
+
+        threads = [threading.Thread(target=run, args=(lane,)) for lane in self._lanes[:n_threads]]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
+
+    def _build_lane(self, lane: _Lane, fragments, TAs, MO_coeff_epsilon: float, sink: Sink | None) -> None:
+        nb = len(lane.bufs)
+        ws = lane.ws
         metric = None if self.tensor.whitened else self.metric
         pending: list[tuple[int, int, np.ndarray, int]] = []  # (fragment, ticket, view, buffer)
         busy: list[Future | None] = [None] * nb  # sink still reading buffer k
 
         def drain_one():
             i, ticket, view, kb = pending.pop(0)
-            self.ws.wait_output(ticket)
+            ws.wait_output(ticket)
             if sink is not None:
                 fut = sink(i, view)
                 busy[kb] = fut if isinstance(fut, Future) else None
 
-        for k, i in enumerate(idx):
+        for k, i in enumerate(fragments):
             TA = TAs[i]
             nmo = TA.shape[1]
             npair = nmo * (nmo + 1) // 2
@@ -156,11 +223,11 @@ class FragmentERIBuilder:
             if busy[kb] is not None:
                 busy[kb].result()
                 busy[kb] = None
-            view = self._bufs[kb][: npair * npair].reshape(npair, npair)
-            q.transform_integral(self.tensor, TA, self.screen, metric, MO_coeff_epsilon, ws=self.ws, out=view,
+            view = lane.bufs[kb][: npair * npair].reshape(npair, npair)
+            q.transform_integral(self.tensor, TA, self.screen, metric, MO_coeff_epsilon, ws=ws, out=view,
                                  synchronize=False)
-            self._note_borderline(i)
-            pending.append((i, self.ws.last_ticket, view, kb))
+            self._note_borderline(i, ws)
+            pending.append((i, ws.last_ticket, view, kb))
             if len(pending) >= nb:
                 drain_one()
         while pending:
@@ -169,11 +236,11 @@ class FragmentERIBuilder:
             if f is not None:
                 f.result()
 
-    def _note_borderline(self, i: int) -> None:
+    def _note_borderline(self, i: int, ws: q.Workspace | None = None) -> None:
         """Screening entries within 1e-12 of the threshold may fall on the other side in an implementation that sums
         in another order (the reference's Eigen GEMM is blocked, FMA and -ffast-math): say so instead of silently
         producing lists that can differ from the reference's."""
-        n = self.ws.borderline
+        n = (ws or self.ws).borderline
         if n:
             self.borderline_total += n
             logger.warning("fragment %d: %d screening entries within 1e-12 of MO_coeff_epsilon; A(i) may differ from "
@@ -191,6 +258,42 @@ class FragmentERIBuilder:
             npair = nmo * (nmo + 1) // 2
             q.transform_integral_device(self.tensor, TAs[i], self.screen, metric, MO_coeff_epsilon, out_dev_ptr,
                                         ld_out or npair, ws=self.ws)
+
+    def build_resident(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, indices: Sequence[int] | None = None,
+                       n_threads: int = 1) -> None:
+        """Transforms with (ij|kl) left in each lane's workspace and nothing delivered: the kernel-only path for
+        BATCHES of small fragments (``n_threads`` lanes overlap on the device).  Asynchronous per lane; callers
+        bracket it with ``ctx.mark`` / ``ctx.synchronize``."""
+        assert self.tensor is not None, "stage() first"
+        idx = list(range(len(TAs))) if indices is None else list(indices)
+        n_threads = max(1, min(int(n_threads), max(len(idx), 1)))
+        while len(self._lanes) < n_threads:
+            self._lanes.append(_Lane(self.ctx))
+        metric = None if self.tensor.whitened else self.metric
+        it, lock = iter(idx), threading.Lock()
+        errors: list[BaseException] = []
+
+        def run(lane):
+            try:
+                while True:
+                    with lock:
+                        i = next(it, None)
+                    if i is None:
+                        return
+                    q.transform_integral_resident(self.tensor, TAs[i], self.screen, metric, MO_coeff_epsilon, ws=lane.ws)
+            except BaseException as e:  # noqa: BLE001
+                errors.append(e)
+
+        if n_threads == 1:
+            run(self._lanes[0])
+        else:
+            threads = [threading.Thread(target=run, args=(lane,)) for lane in self._lanes[:n_threads]]
+            for t in threads:
+                t.start()
+            for t in threads:
+                t.join()
+        if errors:
+            raise errors[0]
 
     def build_jk(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float,
                  densities: Callable[[int], Sequence[np.ndarray]], indices: Sequence[int] | None = None,
@@ -230,27 +333,42 @@ class FragmentERIBuilder:
         return out
 
 
+class _SharedQueue:
+    """Thread-safe iterator over fragment indices (largest first): devices and lanes pull from it dynamically."""
+
+    def __init__(self, order):
+        self._it, self._lock = iter(order), threading.Lock()
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        with self._lock:
+            return next(self._it)
+
+
 def build_all_fragments(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, TAs, MO_coeff_epsilon, sink: Sink,
                         *, devices: Sequence[int] = (0,), whiten: bool = True,
-                        tensors: Sequence[q.SemiSparseSym3DTensor] | None = None) -> None:
-    """One process, one thread per device, fragments handed out dynamically (largest first).  ``tensors`` (one per
-    device, already staged) replaces ``unique_dense_data``."""
+                        tensors: Sequence[q.SemiSparseSym3DTensor] | None = None, n_threads: int = 1) -> None:
+    """One process, one thread per device (x ``n_threads`` lanes each), fragments handed out dynamically (largest
+    first) from one shared queue; every lane keeps its transform -> copy -> sink pipeline full.  ``tensors`` (one per
+    device, already staged) replaces ``unique_dense_data``.  ``sink`` calls are serialised."""
     naux = shape[0]
-    order = sorted(range(len(TAs)), key=lambda i: -fragment_cost(naux, TAs[i].shape[1]))
+    queue = _SharedQueue(sorted(range(len(TAs)), key=lambda i: -fragment_cost(naux, TAs[i].shape[1])))
+    max_nmo = max(t.shape[1] for t in TAs)
     lock = threading.Lock()
     errors: list[BaseException] = []
+
+    def locked_sink(i, G):
+        with lock:
+            return sink(i, G)
 
     def worker(k: int, dev: int):
         try:
             b = FragmentERIBuilder(dev)
             b.stage(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, whiten=whiten,
                     tensor=None if tensors is None else tensors[k])
-            while True:
-                with lock:
-                    if not order:
-                        break
-                    i = order.pop(0)
-                b.build(TAs, MO_coeff_epsilon, sink, indices=[i])
+            b._build_from(queue, max_nmo, TAs, MO_coeff_epsilon, locked_sink, n_threads)
             b.close()
         except BaseException as e:  # noqa: BLE001
             errors.append(e)
@@ -279,7 +397,8 @@ def transform_sparse_DF_integral_b200(mf, Fobjs, auxbasis, file_eri_handler, AO_
     ``get_sparse_P_mu_nu`` are restated in :mod:`quemb_b200.staging` and land the integrals directly in HBM.
     Writes dataset ``fobj.dname`` of shape ``(npair, npair)`` float64 per fragment (``eri_sparse_DF.py:630-631``);
     with ``async_write`` the ``create_dataset`` calls run on a background thread fed from the pinned output ring.
-    ``n_threads`` is accepted for signature compatibility: fragments are pipelined on the device instead."""
+    ``n_threads`` keeps the reference's meaning (``ThreadPoolExecutor(n_threads)``, ``eri_sparse_DF.py:649-653``): that
+    many host threads per device feed fragments concurrently, each on CUDA streams of its own."""
     from pyscf.ao2mo.addons import restore  # noqa: PLC0415
     from pyscf.df.addons import make_auxmol  # noqa: PLC0415
     from quemb.molbe import eri_sparse_DF as ref  # noqa: PLC0415
@@ -316,7 +435,7 @@ def transform_sparse_DF_integral_b200(mf, Fobjs, auxbasis, file_eri_handler, AO_
             tensors = staging.get_sparse_P_mu_nu(mol, auxmol, exch, aux_e2=ref._aux_e2,
                                                  ctx=[q.default_context(d) for d in devices])
             build_all_fragments(None, (naux, nao, nao), lists, L, S_abs, TAs, MO_coeff_epsilon, sink, devices=devices,
-                                whiten=True, tensors=tensors)
+                                whiten=True, tensors=tensors, n_threads=max(1, int(n_threads)))
         else:
             b = FragmentERIBuilder(devices[0])
             metric = q.GPU_MatrixHandle(L, ctx=b.ctx)  # uploaded and block-inverted once, not per fragment

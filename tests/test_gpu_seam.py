@@ -144,7 +144,8 @@ def test_seam_writes_every_fragment_dataset(q, monkeypatch, tmp_path, precompute
     path = tmp_path / "eri_file.h5"
     with open_eri_file(path, "w") as fh:
         transform_sparse_DF_integral_b200(mf, Fobjs, "stub-ri", fh, p.AO_coeff_epsilon, p.MO_coeff_epsilon,
-                                          n_threads=1, precompute_P_mu_nu=precompute, async_write=async_write)
+                                          n_threads=2 if async_write else 1, precompute_P_mu_nu=precompute,
+                                          async_write=async_write)
     assert calls["restore"] == len(Fobjs) and calls["make_auxmol"] == 1 and calls["aux_e2"] > 0
     worst = 0.0
     with open_eri_file(path, "r") as fh:
@@ -188,6 +189,35 @@ def test_build_all_fragments_one_thread_per_device(q):
         for i, TA in enumerate(p.TAs):
             want = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
             assert np.abs(got[i] - want).max() <= 1e-10
+
+
+@pytest.mark.parametrize("n_threads", [2, 4])
+def test_build_with_concurrent_lanes(q, n_threads):
+    """The reference's ``ThreadPoolExecutor(n_threads)`` (eri_sparse_DF.py:649-653): several host threads, each with a
+    workspace / CUDA streams / output ring of its own, share the staged handles; every fragment delivered once."""
+    from quemb_b200 import synthetic as syn
+    from quemb_b200.driver import FragmentERIBuilder
+
+    oracle = _oracle()
+    p = syn.make_chain_problem(n_units=12, ao_per_unit=7, n_end=2, naux=100, frag_halfwidth=1, n_bath=7, sigma=0.6, seed=38)
+    b = FragmentERIBuilder(0, n_host_buffers=2)
+    b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+    want = [oracle.transform_integral(p.unique_dense_data, p.exch_reachable, TA, p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+            for TA in p.TAs]
+    for rep in range(3):
+        errs = {}
+        b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: errs.__setitem__(i, float(np.abs(G - want[i]).max())),
+                n_threads=n_threads)
+        assert sorted(errs) == list(range(len(p.TAs))) and max(errs.values()) <= 1e-10, (rep, errs)
+    b.build_resident(p.TAs, p.MO_coeff_epsilon, n_threads=n_threads)
+    b.ctx.synchronize()
+    # a tensor update after concurrent fragments is ordered behind them (join), the next fragments see it (fork)
+    b.tensor.upload(p.unique_dense_data)
+    b.tensor.whiten(b.metric)
+    errs = {}
+    b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: errs.__setitem__(i, float(np.abs(G - want[i]).max())), n_threads=n_threads)
+    assert max(errs.values()) <= 1e-10
+    b.close()
 
 
 def test_background_writer_on_the_pinned_ring(q, tmp_path):
