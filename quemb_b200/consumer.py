@@ -53,10 +53,10 @@ def initialize_fragments(builder, TAs, MO_coeff_epsilon: float, hf_dm: np.ndarra
     matrices leave the device and no ``eri_file`` round trip is needed.  ``builder`` is a staged
     :class:`quemb_b200.driver.FragmentERIBuilder`.  Returns ``{i: {"veff", "veff0", "e2", "vj", "vk"}}``."""
     idx = list(range(len(TAs))) if indices is None else list(indices)
-    STs = {i: S @ TAs[i] for i in idx}
 
-    def densities(i):
-        P_ = np.asarray((STs[i].T @ hf_dm @ STs[i]).real, dtype=np.float64)
+    def densities(i):  # called per fragment from inside the pipeline: overlaps the device work of that fragment
+        ST = S @ TAs[i]
+        P_ = np.asarray((ST.T @ hf_dm @ ST).real, dtype=np.float64)
         D = np.asarray(rdm_hfs[i], dtype=np.float64)
         return [0.5 * (P_ + P_.T), 0.5 * (D + D.T)]
 

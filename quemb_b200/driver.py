@@ -83,6 +83,7 @@ class FragmentERIBuilder:
         self.ctx = q.default_context(device)
         self.ws = q.Workspace(self.ctx)
         self._lanes: list[_Lane] = [_Lane(self.ctx, self.ws)]
+        self._jk_pool: np.ndarray | None = None
         self.tensor: q.SemiSparseSym3DTensor | None = None
         self.metric: q.GPU_MatrixHandle | None = None
         self.screen = None
@@ -141,6 +142,9 @@ class FragmentERIBuilder:
         self.ctx.synchronize()
         for lane in self._lanes:
             lane.free()
+        if self._jk_pool is not None:
+            _lib.pinned_free(self._jk_pool)
+            self._jk_pool = None
 
     # -- the loop -------------------------------------------------------------------------------------
     def build(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, sink: Sink | None = None,
@@ -305,11 +309,20 @@ class FragmentERIBuilder:
         the full delivery does not apply.  Returns ``{i: [(vj, vk), ...]}``."""
         assert self.tensor is not None, "stage() first"
         idx = list(range(len(TAs))) if indices is None else list(indices)
+        if not idx:
+            return {}
         metric = None if self.tensor.whitened else self.metric
-        dms = {i: [np.asfortranarray(d, dtype=np.float64) for d in densities(i)] for i in idx}
-        total = sum(2 * len(dms[i]) * TAs[i].shape[1] ** 2 for i in idx)
-        pool = _lib.pinned_empty((max(total, 1),))
-        out: dict[int, list[tuple[np.ndarray, np.ndarray]]] = {}
+        # the densities of fragment f are formed on the host AFTER the kernels of f have been enqueued, i.e. while the
+        # device works on f (and still has f-1's J/K queued): host preparation is hidden, not serialised in front
+        first = [np.asfortranarray(d, dtype=np.float64) for d in densities(idx[0])]
+        nd = len(first)
+        total = sum(2 * nd * TAs[i].shape[1] ** 2 for i in idx)
+        if self._jk_pool is None or self._jk_pool.size < total:
+            if self._jk_pool is not None:
+                self.ctx.synchronize()
+                _lib.pinned_free(self._jk_pool)
+            self._jk_pool = _lib.pinned_empty((max(total, 1),))
+        pool = self._jk_pool
         views: dict[int, list[tuple[np.ndarray, np.ndarray]]] = {}
         off = 0
         try:
@@ -317,34 +330,19 @@ class FragmentERIBuilder:
                 nmo = TAs[i].shape[1]
                 q.transform_integral_resident(self.tensor, TAs[i], self.screen, metric, MO_coeff_epsilon, ws=self.ws)
                 self._note_borderline(i)
+                dms = first if i == idx[0] else [np.asfortranarray(d, dtype=np.float64) for d in densities(i)]
+                if len(dms) != nd:
+                    raise ValueError("densities(i) must return the same number of matrices for every fragment")
                 views[i] = []
-                for d in dms[i]:
+                for d in dms:
                     vj = pool[off: off + nmo * nmo].reshape(nmo, nmo, order="F")
                     vk = pool[off + nmo * nmo: off + 2 * nmo * nmo].reshape(nmo, nmo, order="F")
                     off += 2 * nmo * nmo
                     self.ws.jk_enqueue(d, vj, vk)
                     views[i].append((vj, vk))
-            self.ctx.synchronize()
-            for i in idx:
-                out[i] = [(np.array(vj), np.array(vk)) for vj, vk in views[i]]
         finally:
             self.ctx.synchronize()
-            _lib.pinned_free(pool)
-        return out
-
-
-class _SharedQueue:
-    """Thread-safe iterator over fragment indices (largest first): devices and lanes pull from it dynamically."""
-
-    def __init__(self, order):
-        self._it, self._lock = iter(order), threading.Lock()
-
-    def __iter__(self):
-        return self
-
-    def __next__(self):
-        with self._lock:
-            return next(self._it)
+        return {i: [(np.array(vj), np.array(vk)) for vj, vk in views[i]] for i in idx}
 
 
 def build_all_fragments(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, TAs, MO_coeff_epsilon, sink: Sink,

@@ -54,6 +54,9 @@ def make_point(nmo: int, naux: int, max_bytes: float):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--batch", type=int, default=0,
+                    help="additionally time a batch of that many fragments of the point's size through 1/2/4/8 concurrent "
+                         "lanes (FragmentERIBuilder.build_resident): aggregate TF/s of small fragments")
     ap.add_argument("--low", action="store_true", help="only the low end: nmo {20, 50, 100} x naux {500, 2000}")
     ap.add_argument("--out", default="gpurun_out/sweep.json")
     ap.add_argument("--reps", type=int, default=3)
@@ -113,6 +116,28 @@ def main():
             row["JK"] = {"ms": jk_ms, "gbs": nbytes / (jk_ms * 1e-3) / 1e9 if jk_ms else None}
             row["total_ms"] = tot_ms + best["screen"]
             row["total_tflops"] = tot_f / (row["total_ms"] * 1e-3) / 1e12
+            if args.batch:
+                from quemb_b200.driver import FragmentERIBuilder
+
+                bb = FragmentERIBuilder(0)
+                bb.stage(None, None, None, L, S, whiten=False, tensor=T)  # T is whitened already
+                same = [i for i, t in enumerate(p.TAs) if t.shape[1] == n] or [len(p.TAs) - 1]
+                idx = [same[k % len(same)] for k in range(args.batch)]
+                row["batch"] = {"fragments": args.batch, "flops_per_fragment": tot_f}
+                for nt in (1, 2, 4, 8):
+                    bb.build_resident(p.TAs, p.MO_coeff_epsilon, indices=idx, n_threads=nt)  # warm-up (lanes, plans)
+                    ctx.synchronize()
+                    bestb = None
+                    for _ in range(3):
+                        ctx.mark(8)
+                        bb.build_resident(p.TAs, p.MO_coeff_epsilon, indices=idx, n_threads=nt)
+                        ctx.mark(9)
+                        ctx.synchronize()
+                        msb = ctx.mark_elapsed_ms(8, 9)
+                        bestb = msb if bestb is None else min(bestb, msb)
+                    tf = tot_f * args.batch / (bestb * 1e-3) / 1e12
+                    row["batch"][f"lanes_{nt}"] = {"ms": bestb, "tflops": tf, "frac_fp64_peak": tf / peak}
+                del bb
             rows.append(row)
             print(json.dumps(row), flush=True)
             del T, L, S, G, p
