@@ -27,6 +27,8 @@
 // 16 distinct bank pairs.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "dmma_core.cuh"
 #include "kernels.cuh"
 
@@ -205,8 +207,10 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
                         if (p.accumulate) {
                             atomicAdd_system(&Gout[row + p.ldg * (col + e)], v);
                         } else {
-                            Gout[row + p.ldg * (col + e)] = v;
-                            if (offdiag) Gout[(col + e) + p.ldg * row] = v;
+                            // streaming stores (evict-first): the 8 npair^2 bytes of G pass through L2 once and must
+                            // not push out the X panels the resident band of tiles keeps re-reading
+                            __stcs(&Gout[row + p.ldg * (col + e)], v);
+                            if (offdiag) __stcs(&Gout[(col + e) + p.ldg * row], v);
                         }
                     }
                 }
@@ -329,10 +333,21 @@ cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
 }
 
 // Lower-triangular tile list in bands of GROUP row tiles: inside a band the column tile is the slow
-// index, so the resident wave touches <= GROUP row panels and ~148/GROUP column panels.
+// index, so the resident wave touches <= GROUP row panels and ~148/GROUP column panels.  DRAM reads of X are
+// ~ nt^2 / (2 GROUP) panels as long as the GROUP row panels of a band (GROUP x 128 x naux x 8 bytes) stay in L2.
+int gram_tile_group()
+{
+    static const int group = [] {
+        int g = 12;
+        if (const char *e = std::getenv("QEMB_K3_GROUP")) g = std::atoi(e);
+        return g < 1 ? 1 : (g > 148 ? 148 : g);
+    }();
+    return group;
+}
+
 int64_t build_gram_tiles(int nt, int2 *out)
 {
-    constexpr int GROUP = 12;
+    const int GROUP = gram_tile_group();
     int64_t n = 0;
     for (int i0 = 0; i0 < nt; i0 += GROUP) {
         const int i1 = (i0 + GROUP < nt) ? i0 + GROUP : nt;
