@@ -374,6 +374,12 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
 
     peak_burst, peak_sust = fp64_peak_tflops(torch) if rank == 0 else (0.0, 0.0)
     cores = host_cores()
+    try:  # torchrun exports OMP_NUM_THREADS=1: give numpy's BLAS (synthetic-data generation only) this rank's share
+        from threadpoolctl import threadpool_limits
+
+        threadpool_limits(limits=max(1, cores // world))
+    except Exception:  # noqa: BLE001
+        pass
     host_bw = host_write_bandwidth(cores) if rank == 0 else None
     barrier()
 

@@ -345,6 +345,20 @@ class FragmentERIBuilder:
         return {i: [(np.array(vj), np.array(vk)) for vj, vk in views[i]] for i in idx}
 
 
+class _SharedQueue:
+    """Thread-safe iterator over fragment indices (largest first): devices and lanes pull from it dynamically."""
+
+    def __init__(self, order):
+        self._it, self._lock = iter(order), threading.Lock()
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        with self._lock:
+            return next(self._it)
+
+
 def build_all_fragments(unique_dense_data, shape, exch_reachable, L_PQ, S_abs, TAs, MO_coeff_epsilon, sink: Sink,
                         *, devices: Sequence[int] = (0,), whiten: bool = True,
                         tensors: Sequence[q.SemiSparseSym3DTensor] | None = None, n_threads: int = 1) -> None:

@@ -284,3 +284,105 @@ def test_world_size_2_gloo_fused_peer_accumulate(tmp_path):
     assert sorted(r0["owned"] + r1["owned"]) == list(range(res["nfrag"]))
     errs = {**r0["errs"], **r1["errs"]}
     assert len(errs) == res["nfrag"] and max(errs.values()) <= 1e-10, errs
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the fragment loop itself (lanes, shared queue, buffer hand-back) with the device replaced by a host fake
+# ---------------------------------------------------------------------------------------------------------------------
+class _FakeDevice:
+    """Stands in for quemb_b200.eri_sparse_DF inside quemb_b200.driver: transforms write a recognisable matrix into
+    the caller's pinned view, tickets complete in order.  Only the HOST logic of driver.py is under test here."""
+
+    def __init__(self):
+        import threading
+
+        self.lock = threading.Lock()
+        self.calls = []
+
+    class Ctx:
+        device = 0
+
+        def synchronize(self):
+            pass
+
+    class WS:
+        def __init__(self, ctx=None):
+            self.last_ticket = 0
+            self.borderline = 0
+            self.waited = []
+
+        def wait_output(self, ticket):
+            self.waited.append(ticket)
+
+    class Tensor:
+        whitened = True
+
+    def install(self, monkeypatch):
+        from quemb_b200 import _lib, driver
+
+        fake = self
+        monkeypatch.setattr(driver.q, "default_context", lambda d=None: _FakeDevice.Ctx())
+        monkeypatch.setattr(driver.q, "Workspace", _FakeDevice.WS)
+        monkeypatch.setattr(driver.q, "output_ring_depth", lambda: 3)
+        monkeypatch.setattr(_lib, "pinned_empty", lambda shape, dtype=np.float64: np.empty(shape, dtype=dtype))
+        monkeypatch.setattr(_lib, "pinned_free", lambda a: None)
+
+        def transform_integral(tensor, TA, screen, metric, eps, ws=None, out=None, synchronize=True):
+            out[...] = float(TA[0, 0])
+            ws.last_ticket += 1
+            with fake.lock:
+                fake.calls.append((id(ws), int(TA[0, 0])))
+            return out
+
+        monkeypatch.setattr(driver.q, "transform_integral", transform_integral)
+
+
+@pytest.mark.parametrize("n_threads", [1, 3])
+def test_fragment_loop_delivers_every_fragment_once(monkeypatch, n_threads):
+    from concurrent.futures import ThreadPoolExecutor
+
+    from quemb_b200 import driver
+
+    fake = _FakeDevice()
+    fake.install(monkeypatch)
+    TAs = [np.full((4, 2 + (i % 3)), float(i)) for i in range(11)]  # fragment i is recognisable by TA[0, 0] = i
+    b = driver.FragmentERIBuilder(0, n_host_buffers=2)
+    b.tensor, b.metric, b.screen = _FakeDevice.Tensor(), None, None
+    seen = {}
+    pool = ThreadPoolExecutor(max_workers=1)
+
+    def sink(i, G):  # returns a Future: the buffer must stay untouched until it is done
+        def check():
+            import time
+
+            time.sleep(0.002)
+            npair = TAs[i].shape[1] * (TAs[i].shape[1] + 1) // 2
+            assert G.shape == (npair, npair) and np.all(G == float(i)), (i, G)
+            seen[i] = seen.get(i, 0) + 1
+            return i
+
+        return pool.submit(check)
+
+    b.build(TAs, 1e-5, sink, n_threads=n_threads)
+    pool.shutdown()
+    assert seen == {i: 1 for i in range(len(TAs))}
+    assert len({w for w, _ in fake.calls}) == n_threads  # one workspace per lane
+    assert len(b._lanes) >= n_threads and all(len(l.bufs) == 2 for l in b._lanes[:n_threads])
+    b.close()
+
+
+def test_build_all_fragments_shared_queue_largest_first(monkeypatch):
+    from quemb_b200 import driver
+
+    fake = _FakeDevice()
+    fake.install(monkeypatch)
+    monkeypatch.setattr(driver.FragmentERIBuilder, "stage", lambda self, *a, **k: (setattr(self, "tensor", _FakeDevice.Tensor())))
+    TAs = [np.full((4, n), float(i)) for i, n in enumerate([2, 5, 3, 6, 4, 2, 7])]
+    got = []
+    driver.build_all_fragments(None, (8, 4, 4), None, None, None, TAs, 1e-5, lambda i, G: got.append(i),
+                               devices=(0, 1), n_threads=2)
+    assert sorted(got) == list(range(len(TAs)))
+    order = [i for _, i in fake.calls]
+    assert order[0] == 6 and set(order[:2]) == {6, 3}  # largest fragments are handed out first
+    with pytest.raises(ValueError):
+        driver.FragmentERIBuilder(0, n_host_buffers=0)
