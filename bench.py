@@ -765,7 +765,8 @@ def sharded_extra(args, torch, dist, q, rank: int, world: int, local_rank: int, 
     torch.cuda.empty_cache()
     # (b) oversize fragments
     t0 = time.perf_counter()
-    p = syn.sweep_point(args.sharded_nmo, args.sharded_naux, max_bytes=args.sharded_max_gb * 1e9, matmul=gpu_matmul)
+    p = syn.sweep_point(args.sharded_nmo, args.sharded_naux, max_bytes=args.sharded_max_gb * 1e9, matmul=gpu_matmul,
+                        device_linalg=True)
     gen_s = time.perf_counter() - t0
     nf = args.sharded_fragments
     frags = [len(p.TAs) - 1 - k for k in range(nf)]

@@ -97,11 +97,26 @@ def gaussian_S_abs(r: np.ndarray, sigma: float) -> np.ndarray:
     return S
 
 
-def metric_cholesky(naux: int, cond: float, rng) -> np.ndarray:
+def metric_cholesky(naux: int, cond: float, rng, device_linalg: bool = False) -> np.ndarray:
     """cholesky(Q diag(logspace(0,-log10 cond)) Q^T, lower=True) with a random
-    orthogonal Q — an RI-metric-like ill-conditioned SPD matrix."""
-    Q, _ = np.linalg.qr(rng.standard_normal((naux, naux)))
+    orthogonal Q — an RI-metric-like ill-conditioned SPD matrix.  ``device_linalg``: QR / products / Cholesky with
+    torch on the current CUDA device (synthetic-data generation of the big timing cases only; naux = 8000 costs a
+    minute per rank on a few host threads)."""
+    A = rng.standard_normal((naux, naux))
     ev = np.logspace(0.0, -np.log10(cond), naux)
+    if device_linalg:
+        import torch
+
+        Ad = torch.from_numpy(A).cuda()
+        Qd, _ = torch.linalg.qr(Ad)
+        PQd = (Qd * torch.from_numpy(ev).cuda()) @ Qd.T
+        PQd = 0.5 * (PQd + PQd.T)
+        Ld = torch.linalg.cholesky(PQd)
+        L = np.asfortranarray(Ld.cpu().numpy())
+        del Ad, Qd, PQd, Ld
+        torch.cuda.empty_cache()
+        return L
+    Q, _ = np.linalg.qr(A)
     PQ = (Q * ev) @ Q.T
     PQ = 0.5 * (PQ + PQ.T)
     return np.asfortranarray(scipy.linalg.cholesky(PQ, lower=True))
@@ -173,6 +188,7 @@ def make_chain_problem(
     AO_coeff_epsilon: float = 1e-10,
     name: str = "chain",
     matmul=None,
+    device_linalg: bool = False,
 ) -> Problem:
     """Alkane-like chain. One fragment per unit (centre unit +- halfwidth units,
     clipped at the ends — edge fragments are smaller, like BE-n on a chain)."""
@@ -181,7 +197,7 @@ def make_chain_problem(
     nao = len(r)
     S_abs = gaussian_S_abs(r, sigma)
     exch = get_AO_per_AO(S_abs, AO_coeff_epsilon)
-    L = metric_cholesky(naux, cond, rng)
+    L = metric_cholesky(naux, cond, rng, device_linalg=device_linalg)
     M = make_P_mu_nu(r, sigma, exch, L, rng, matmul=matmul)
     unit_of_ao = np.concatenate(
         [
@@ -290,7 +306,8 @@ def _fit_sigma(r: np.ndarray, naux: int, max_bytes: float, sigma: float, shrink:
         sigma *= shrink
 
 
-def sweep_point(nmo: int, naux: int, max_bytes: float = 3e9, matmul=None, cond: float = 1e8) -> Problem:
+def sweep_point(nmo: int, naux: int, max_bytes: float = 3e9, matmul=None, cond: float = 1e8,
+                device_linalg: bool = False) -> Problem:
     """One point of the synthetic sweep (SURVEY 8d "sweep": nmo in 20..400 x naux in 500..8000, nao ~ 4 nmo, one
     fragment): a chain whose interior fragment (``TAs[-1]``) has 3 units (55 % of nmo) + bath tails (45 %)."""
     a = max(2, round(0.55 * nmo / 3))
@@ -299,7 +316,7 @@ def sweep_point(nmo: int, naux: int, max_bytes: float = 3e9, matmul=None, cond: 
     sigma = _fit_sigma(chain_centres(n_units, a, 0, np.random.default_rng(1)), naux, max_bytes, 0.94)
     p = make_chain_problem(n_units=n_units, ao_per_unit=a, n_end=0, naux=naux, frag_halfwidth=1, n_bath=n_bath,
                            sigma=sigma, cond=cond, seed=SEED + nmo + naux, n_frag=n_units // 2 + 1, matmul=matmul,
-                           name=f"sweep nmo{nmo} naux{naux}")
+                           name=f"sweep nmo{nmo} naux{naux}", device_linalg=device_linalg)
     p.meta["sigma"] = sigma
     return p
 

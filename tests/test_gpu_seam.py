@@ -144,7 +144,7 @@ def test_seam_writes_every_fragment_dataset(q, monkeypatch, tmp_path, precompute
     path = tmp_path / "eri_file.h5"
     # on the fly the AO screening is per fragment; a coarser threshold makes the source sets proper subsets of the AOs
     # (partial dicts, the case ADVICE r1 flagged), every pair they keep is still inside the stub's screened set
-    ao_eps = p.AO_coeff_epsilon if precompute else 1e-3
+    ao_eps = p.AO_coeff_epsilon if precompute else 0.3
     with open_eri_file(path, "w") as fh:
         transform_sparse_DF_integral_b200(mf, Fobjs, "stub-ri", fh, ao_eps, p.MO_coeff_epsilon,
                                           n_threads=2 if async_write else 1, precompute_P_mu_nu=precompute,
