@@ -342,7 +342,7 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
 
     from quemb_b200 import _lib, consumer
     from quemb_b200 import eri_sparse_DF as q
-    from quemb_b200.driver import FragmentERIBuilder, fragment_cost, partition_lpt
+    from quemb_b200.driver import DistributedQueue, FragmentERIBuilder, fragment_cost, partition_lpt
 
     if not torch.cuda.is_available() or _lib.device_count() == 0:
         raise SystemExit("bench.py: no CUDA device -- the B200 arm has no CPU fallback (use --impl reference)")
@@ -456,14 +456,26 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
 
     # ---- e2e: host buffers in, pinned host buffers out ------------------------------------------------
     result_bytes = sum(8 * (t.shape[1] * (t.shape[1] + 1) // 2) ** 2 for t in (p.TAs[i] for i in mine))
-    # How a host-bound (ij|kl) travels.  Triangle + mirror on the host cores halves the PCIe bytes (the limit of ONE
-    # GPU); with several GPUs every rank has its own PCIe link but the ranks share the host cores, so the full
-    # square goes over PCIe and no CPU pass is needed (profiles/e2e_timeline_r2_*.json).
+    # How a host-bound (ij|kl) travels: the lower triangle always crosses PCIe; of the upper triangle a fraction crosses
+    # PCIe as well and the rest is rebuilt by the library's host threads.  "auto": every rank measures its own copy
+    # rate and mirror rate at the same moment (all ranks, mutual contention included) and balances the two
+    # (qemb_ctx_autotune_output); "triangle" / "full" force the two extremes.
     out_mode = args.e2e_output
+    barrier()
     if out_mode == "auto":
-        out_mode = "triangle" if world == 1 else "full"
-    ctx.set_output_mode(out_mode == "triangle")
+        tuned = b.tune_output()
+    else:
+        ctx.set_output_mode(out_mode == "triangle")
+        ctx.set_full_column_fraction(0.0)
+        tuned = {"d2h_gbs": None, "mirror_gbs": None, "upper_fraction_over_pcie": 0.0 if out_mode == "triangle" else 1.0}
+    tuned_all = [tuned]
+    if dist is not None:
+        tuned_all = [None] * world
+        dist.all_gather_object(tuned_all, tuned)
     checks = []
+    order_all = sorted(range(nfrag), key=lambda i: (-costs[i], i))
+    taken_counts = []
+    qcount = [0]
 
     def sink(i, G):
         checks.append(float(G[0, 0]) + float(G[-1, -1]))  # the step's result is read on the host
@@ -482,7 +494,15 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
         ta = time.perf_counter()
         stage_from_host()
         tb = time.perf_counter()
-        b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
+        if dist is None:
+            b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
+        else:
+            # fragments are handed out dynamically across the ranks (largest first, an atomic counter in the process
+            # group's store): the ranks of one box do not drain their outputs at the same rate (PCIe topology, host
+            # share), and delivery, not the kernels, bounds this number
+            qcount[0] += 1
+            taken = b.build_dynamic(p.TAs, p.MO_coeff_epsilon, sink, DistributedQueue(dist, order_all, f"e2e{qcount[0]}"))
+            taken_counts.append(len(taken))
         tl["upload+stage_s"] += tb - ta
         tl["build_s"] += time.perf_counter() - tb
 
@@ -504,9 +524,13 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
     t_e2e = max_over_ranks(ctx.mark_elapsed_ms(2, 3) * 1e-3) / e2e_steps
     wall_e2e = max_over_ranks(wall_e2e)
     tl_max = {k: max_over_ranks(v / e2e_steps) for k, v in tl.items()}
+    frag_taken = [len(mine)]
+    if dist is not None:
+        frag_taken = [None] * world
+        dist.all_gather_object(frag_taken, taken_counts[-1] if taken_counts else 0)
     clocks = sampler.stop() if sampler else None
     h2d_all, d2h_all = sum_over_ranks(float(h2d)), sum_over_ranks(float(d2h_moved))
-    result_all = sum_over_ranks(float(result_bytes))
+    result_all = float(sum(8 * (t.shape[1] * (t.shape[1] + 1) // 2) ** 2 for t in p.TAs))
     launches_all = int(sum_over_ranks(float(launches)))
 
     # aggregate device->host rate the box can absorb (all ranks copy 2 GiB to pinned memory at once): the delivery
@@ -679,6 +703,8 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
         "e2e": {"value": t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
                 "result_bytes_per_step": int(result_all), "wall_s": wall_e2e, "steps": e2e_steps,
                 "output_mode": out_mode,
+                "autotune_per_rank": tuned_all,
+                "fragments_taken_per_rank_last_step": frag_taken,
                 "timeline_max_over_ranks": tl_max,
                 "host": {"cores": cores, "threads_per_rank": q_host_threads(_lib), "dram_write_gbs": host_write,
                          "dram_copy_gbs": (host_bw or {}).get("copy_gbs"), "d2h_aggregate_gbs": d2h_gbs_all},
@@ -689,10 +715,11 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
                 "kernel_fraction": t_dev / t_e2e if t_e2e else None,
                 "note": ("includes upload of (P|mu nu)+L+S_abs from pageable host memory"
                          + (" (1/N of the columns per rank, shares exchanged over NVLink)" if world > 1 else "")
-                         + ", metric application, all fragments, every full npair x npair G delivered in pinned host "
-                         "memory (" + ("lower triangle over PCIe, upper triangle rebuilt by the library's host threads"
-                                       if out_mode == "triangle" else "full square over every rank's own PCIe link, no CPU pass")
-                         + ") inside the timed region")},
+                         + ", metric application, all fragments"
+                         + (" (handed out dynamically across the ranks)" if world > 1 else "")
+                         + ", every full npair x npair G delivered in pinned host memory (lower triangle over PCIe; of the "
+                         "upper triangle the per-rank fraction autotune_per_rank[r].upper_fraction_over_pcie crosses PCIe "
+                         "too, the rest is rebuilt by the library's host threads) inside the timed region")},
         "e2e_consumer": {"value": t_cons, "unit": UNIT, "h2d_bytes_per_step": int(cons_h2d), "d2h_bytes_per_step": int(cons_d2h),
                          "steps": cons_steps, "checksum": cons_check,
                          "note": "same host inputs, same transforms; get_veff + update_ebe_hf two-electron sums of every "

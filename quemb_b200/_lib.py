@@ -66,6 +66,7 @@ _SIGS = {
     "qemb_output_ring_depth": (c_int, []),
     "qemb_host_bandwidth": (c_int, [c_i64, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
     "qemb_ctx_stream_handoff": (c_int, [c_p, c_p, c_int]),
+    "qemb_ctx_autotune_output": (c_int, [c_p, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
     "qemb_device_count": (c_int, [ctypes.POINTER(c_int)]),
     "qemb_ctx_create": (c_int, [c_int, ctypes.POINTER(c_p)]),
     "qemb_ctx_destroy": (None, [c_p]),

@@ -649,6 +649,76 @@ extern "C" int qemb_host_bandwidth(int64_t bytes, double *write_gbs, double *cop
     return QEMB_OK;
 }
 
+// Self-tuning of how a host-bound (ij|kl) travels (output mode 1 + full-column fraction): times a device -> host copy
+// into pinned memory on the copy stream WHILE the library's host threads mirror a test matrix, i.e. both rates under
+// the contention they will see in a build (other ranks of the node calling this at the same moment included), and
+// balances the two: with P = copy rate and M = mirror rate (bytes of upper triangle produced per second), sending the
+// fraction f = (P - M) / (P + M) of the upper triangle over PCIe and mirroring the rest makes both finish together
+// (lower triangle ~ upper triangle ~ U bytes: (U + f U) / P = (1 - f) U / M).  f <= 0: pure triangle transfer;
+// f >= 0.9: the full square crosses PCIe and no CPU pass is made.
+extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie)
+{
+    REQ(c != nullptr, "null ctx");
+    DeviceGuard g(c->device);
+    const int64_t n = 6144;                       // mirror test matrix: 6144^2 doubles = 302 MB
+    const size_t mbytes = (size_t)n * n * 8, cbytes = 256u << 20;
+    const int ncopies = 6;
+    void *hm = nullptr, *hc = nullptr, *dv = nullptr;
+    cudaError_t e = cudaMallocHost(&hm, mbytes);
+    if (e == cudaSuccess) e = cudaMallocHost(&hc, cbytes);
+    if (e == cudaSuccess) e = cudaMalloc(&dv, cbytes);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        if (hm) cudaFreeHost(hm);
+        if (hc) cudaFreeHost(hc);
+        if (dv) cudaFree(dv);
+        return fail(QEMB_ENOMEM, std::string("autotune buffers: ") + cudaGetErrorString(e));
+    }
+    std::memset(hm, 0, mbytes);
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    CU(cudaMemsetAsync(dv, 0, cbytes, c->copy));
+    CU(cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy)); // warm-up
+    CU(cudaStreamSynchronize(c->copy));
+    qemb_host_mirror_lower(static_cast<double *>(hm), n, 1024);             // warm-up (threads, page faults)
+    CU(cudaEventRecord(e0, c->copy));
+    for (int i = 0; i < ncopies; ++i) CU(cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy));
+    CU(cudaEventRecord(e1, c->copy));
+    const auto t0 = std::chrono::steady_clock::now();
+    int reps = 0;
+    do {  // keep the host threads mirroring for as long as the copies run
+        qemb_host_mirror_lower(static_cast<double *>(hm), n, n);
+        ++reps;
+    } while (cudaEventQuery(e1) == cudaErrorNotReady && reps < 64);
+    const double tm = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    (void)cudaGetLastError();
+    CU(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFreeHost(hm);
+    cudaFreeHost(hc);
+    cudaFree(dv);
+    const double P = (double)ncopies * (double)cbytes / (ms * 1e-3) / 1e9;
+    const double M = (double)reps * (double)n * (double)(n - 1) / 2.0 * 8.0 / tm / 1e9;
+    double f = (P - M) / (P + M);
+    f = f < 0.0 ? 0.0 : f;
+    if (f >= 0.9) {
+        c->out_mode = 0;
+        c->full_frac = 0.0;
+        f = 1.0;
+    } else {
+        c->out_mode = 1;
+        c->full_frac = 1.0 - std::sqrt(1.0 - f); // whole columns [cs, n) carry 1 - (cs / n)^2 of the upper triangle
+    }
+    if (d2h_gbs) *d2h_gbs = P;
+    if (mirror_gbs) *mirror_gbs = M;
+    if (upper_fraction_pcie) *upper_fraction_pcie = f;
+    return QEMB_OK;
+}
+
 // Orders an EXTERNAL stream (e.g. torch's current stream, which NCCL collectives are enqueued on) against the
 // library's compute stream without a host synchronisation.  direction 0: work enqueued on `external_stream` after
 // this call waits for everything enqueued on the compute stream so far; direction 1: the reverse.
@@ -1195,7 +1265,10 @@ extern "C" int qemb_workspace_create(qemb_ctx *ctx, qemb_workspace **out)
         CU(cudaEventCreateWithFlags(&w->slot[i].consumed, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&w->slot[i].ta_ready, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&w->g_copied[i], cudaEventDisableTiming));
-        for (int k = i; k < OUT_RING; k += 2) CU(cudaEventCreateWithFlags(&w->out_done[k], cudaEventDisableTiming));
+        // blocking sync: the caller's thread sleeps while a multi-GB (ij|kl) drains instead of spinning on a host core that
+        // the mirror threads (and, with several ranks per node, the other ranks) need
+        for (int k = i; k < OUT_RING; k += 2)
+            CU(cudaEventCreateWithFlags(&w->out_done[k], cudaEventDisableTiming | cudaEventBlockingSync));
     }
     for (int i = 0; i < 5; ++i) CU(cudaEventCreate(&w->ev[i]));
     for (int i = 0; i < 2; ++i) CU(cudaEventCreate(&w->evs[i]));
@@ -1884,7 +1957,8 @@ void CUDART_CB mirror_callback(void *arg)
                                                                  // transposed image is not delivered by PCIe
     int64_t chunk = 0, ntasks = 0;
     if (rows > 0 && width > 0) {
-        chunk = std::max<int64_t>(256, ((int64_t)(2 << 20) / (8 * width) + 15) / 16 * 16); // ~2 MB per task
+        // ~2 MB per task, whole 256-row passes of the tiled mirror (host_pool.cpp)
+        chunk = std::max<int64_t>(256, ((int64_t)(2 << 20) / (8 * width) + 255) / 256 * 256);
         ntasks = (rows + chunk - 1) / chunk;
     }
     {

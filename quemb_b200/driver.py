@@ -131,6 +131,19 @@ class FragmentERIBuilder:
     def _bufs(self) -> list[np.ndarray]:
         return self._lanes[0].bufs
 
+    def tune_output(self) -> dict[str, float]:
+        """Let the library balance PCIe against the host mirror threads for this rank (``Context.autotune_output``);
+        call on all ranks of a node at the same moment."""
+        return self.ctx.autotune_output()
+
+    def build_dynamic(self, TAs: Sequence[np.ndarray], MO_coeff_epsilon: float, sink: Sink | None, queue,
+                      n_threads: int = 1) -> list[int]:
+        """:meth:`build` over a queue shared with other builders (:class:`DistributedQueue` across ranks): returns
+        the fragments this builder ended up transforming."""
+        assert self.tensor is not None, "stage() first"
+        self._build_from(queue, max(t.shape[1] for t in TAs), TAs, MO_coeff_epsilon, sink, n_threads)
+        return list(getattr(queue, "taken", []))
+
     def reserve_host(self, max_nmo: int, lanes: int = 1) -> None:
         npair = max_nmo * (max_nmo + 1) // 2
         while len(self._lanes) < lanes:
@@ -343,6 +356,33 @@ class FragmentERIBuilder:
         finally:
             self.ctx.synchronize()
         return {i: [(np.array(vj), np.array(vk)) for vj, vk in views[i]] for i in idx}
+
+
+class DistributedQueue:
+    """Fragment indices handed out dynamically ACROSS RANKS (one process per GPU): an atomic counter in the process
+    group's key-value store (``store.add``), so a rank whose PCIe link or host share is faster simply takes more
+    fragments -- the fragment-parallel build has no other inter-rank traffic.  Every rank constructs it with the same
+    ``order`` (largest first) and the same ``name``; iterate once."""
+
+    def __init__(self, dist, order: Sequence[int], name: str, store=None):
+        if store is None:
+            from torch.distributed import distributed_c10d as c10d  # noqa: PLC0415
+
+            store = c10d._get_default_store()
+        self._store, self._order, self._key = store, list(order), f"qemb_fragment_queue/{name}"
+        self._lock = threading.Lock()
+        self.taken: list[int] = []
+
+    def __iter__(self):
+        return self
+
+    def __next__(self) -> int:
+        with self._lock:
+            k = int(self._store.add(self._key, 1)) - 1
+            if k >= len(self._order):
+                raise StopIteration
+            self.taken.append(self._order[k])
+            return self._order[k]
 
 
 class _SharedQueue:

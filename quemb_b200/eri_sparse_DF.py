@@ -86,6 +86,14 @@ class Context:
         by the host threads."""
         check(lib().qemb_ctx_set_full_column_fraction(self._h, c_dbl(frac)))
 
+    def autotune_output(self) -> dict[str, float]:
+        """Measure this context's device->host copy rate and the host threads' mirror rate under mutual contention
+        and set output mode / full-column fraction so that both finish together (``qemb_ctx_autotune_output``).
+        With several ranks per node call it on all of them at the same moment (after a barrier)."""
+        p, m, f = c_dbl(), c_dbl(), c_dbl()
+        check(lib().qemb_ctx_autotune_output(self._h, ctypes.byref(p), ctypes.byref(m), ctypes.byref(f)))
+        return {"d2h_gbs": p.value, "mirror_gbs": m.value, "upper_fraction_over_pcie": f.value}
+
     def set_k3_int8_slices(self, slices: int) -> None:
         """Opt-in K3 on the int8 tensor cores (0 = FP64 path, the default and the parity reference; 5 .. 8 integer
         slices of 8 bits: about 1e-11 / 2e-13 / FP64 rounding level (7, 8) of max|(ij|kl)| from the exact product, cost

@@ -21,13 +21,15 @@ import numpy as np
 import bench
 from quemb_b200 import _lib
 from quemb_b200 import eri_sparse_DF as q
-from quemb_b200.driver import FragmentERIBuilder, fragment_cost, partition_lpt
+from quemb_b200.driver import DistributedQueue, FragmentERIBuilder, fragment_cost, partition_lpt
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--modes", default="triangle:sharded,full:sharded",
-                    help="comma list of <output>:<upload>; output = triangle | full, upload = replicated | sharded")
+                    help="comma list of <output>:<upload>[:dynamic]; output = triangle | full | auto (per-rank balance of "
+                         "PCIe against the host mirror, qemb_ctx_autotune_output), upload = replicated | sharded, "
+                         "dynamic = fragments handed out across ranks from a shared counter instead of a static partition")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--buffers", type=int, default=3)
     ap.add_argument("--out", default="gpurun_out/e2e_timeline.jsonl")
@@ -78,8 +80,17 @@ def main():
         log["sink_s"] = log.get("sink_s", 0.0) + time.perf_counter() - t
 
     for mode in args.modes.split(","):
-        output, upload = mode.split(":")
-        ctx.set_output_mode(output == "triangle")
+        parts = mode.split(":")
+        output, upload, dynamic = parts[0], parts[1], len(parts) > 2 and parts[2] == "dynamic" and dist is not None
+        barrier()
+        tuned = None
+        if output == "auto":
+            tuned = b.tune_output()
+        else:  # "triangle", "full", or "triangle@<fraction of the columns that cross PCIe whole>"
+            kind, _, frac = output.partition("@")
+            ctx.set_output_mode(kind == "triangle")
+            ctx.set_full_column_fraction(float(frac) if frac else 0.0)
+        order_all = sorted(range(len(p.TAs)), key=lambda i: (-costs[i], i))
         rows = []
         for rep in range(args.reps + 1):
             log.clear()
@@ -100,7 +111,11 @@ def main():
                 b.stage_distributed(p.unique_dense_data, p.L_PQ, p.S_abs, dist, tensor=T)
             ctx.synchronize()
             t2 = time.perf_counter()
-            b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
+            done = mine
+            if dynamic:
+                done = b.build_dynamic(p.TAs, p.MO_coeff_epsilon, sink, DistributedQueue(dist, order_all, f"{mode}/{rep}"))
+            else:
+                b.build(p.TAs, p.MO_coeff_epsilon, sink, indices=mine)
             ctx.synchronize()
             t3 = time.perf_counter()
             barrier()
@@ -108,20 +123,21 @@ def main():
             x1 = ctx.transfer_bytes
             if rep == 0:
                 continue  # warm-up
-            res = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in mine)
-            rows.append({"rep": rep, "upload_s": t1 - t0, "stage_s": t2 - t1, "build_s": t3 - t2, "total_s": t3 - t0,
+            res = sum(8 * (p.TAs[i].shape[1] * (p.TAs[i].shape[1] + 1) // 2) ** 2 for i in done)
+            rows.append({"rep": rep, "fragments_done": len(done), "upload_s": t1 - t0, "stage_s": t2 - t1, "build_s": t3 - t2, "total_s": t3 - t0,
                          "all_ranks_done_s": t4 - t0, **{k: v for k, v in log.items()},
                          "h2d_gb": (x1[0] - x0[0]) / 1e9, "d2h_gb": (x1[1] - x0[1]) / 1e9, "result_gb": res / 1e9,
                          "delivery_gbs": res / (t3 - t2) / 1e9})
         mean = {k: float(np.mean([r[k] for r in rows])) for k in rows[0] if k != "rep"}
-        mine_rec = {"rank": rank, "fragments": len(mine), "host_threads": bench.q_host_threads(_lib),
+        mine_rec = {"rank": rank, "fragments": len(mine), "autotune": tuned, "host_threads": bench.q_host_threads(_lib),
                     "host_write_gbs_rank_threads": hw, "host_copy_gbs_rank_threads": hc, "mean": mean, "reps": rows}
         allrec = [mine_rec]
         if dist is not None:
             allrec = [None] * world
             dist.all_gather_object(allrec, mine_rec)
         if rank == 0:
-            line = {"n_gpus": world, "output": output, "upload": upload, "buffers": args.buffers,
+            line = {"n_gpus": world, "output": output, "upload": upload, "dynamic_queue": bool(dynamic), "buffers": args.buffers,
+                    "full_column_fraction_env": os.environ.get("QEMB_FULL_COLUMN_FRACTION"),
                     "cores": len(os.sched_getaffinity(0)),
                     "e2e_s_max_over_ranks": max(r["mean"]["total_s"] for r in allrec),
                     "all_ranks_done_s": max(r["mean"]["all_ranks_done_s"] for r in allrec),

@@ -11,7 +11,13 @@ for G in 12 16 24 32 48; do
     --log-file gpurun_out/r2c6_k3_group_$G.csv python scripts/profile_k3.py 25425 2716 1 > /dev/null 2>&1; echo "ncu group $G exit $?"
   grep -E "dram__bytes|hit_rate|gpu__time" gpurun_out/r2c6_k3_group_$G.csv | awk -F'","' '{print $(NF-2), $(NF-1), $NF}' | sed "s/^/group $G: /" | tee -a gpurun_out/r2c6_k3_group_traffic.txt
 done
-# N = 1 end to end: how much of the upper triangle should cross PCIe instead of being mirrored by the host threads
-for F in 0 0.1 0.16 0.22 0.3; do
-  QEMB_FULL_COLUMN_FRACTION=$F timeout 300 python scripts/e2e_timeline.py --modes triangle:sharded --reps 2 --out gpurun_out/r2c6_e2e_hybrid.jsonl 2>/dev/null | grep '^{' | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('full_frac $F', 'e2e', round(d['e2e_s_max_over_ranks'],3), 'build', round(d['rank0_mean']['build_s'],3), 'd2h_gb', round(d['rank0_mean']['d2h_gb'],1))" | tee -a gpurun_out/r2c6_e2e_hybrid.txt
-done
+# N = 1 end to end: fixed fractions of whole columns against the self-tuned balance (new AVX-512 tiled mirror)
+timeout 600 python scripts/e2e_timeline.py --modes triangle@0:sharded,triangle@0.05:sharded,triangle@0.1:sharded,triangle@0.16:sharded,triangle@0.25:sharded,auto:sharded,full:sharded --reps 2 --out gpurun_out/r2c6_e2e_hybrid.jsonl > gpurun_out/r2c6_e2e_hybrid.log 2>&1; echo "hybrid exit $?"
+python - <<'PY'
+import json
+for l in open('gpurun_out/r2c6_e2e_hybrid.jsonl'):
+    d = json.loads(l); r = d['ranks'][0]
+    print(d['output'], 'e2e', round(d['e2e_s_max_over_ranks'], 3), 'build', round(r['mean']['build_s'], 3), 'd2h_gb', round(r['mean']['d2h_gb'], 1), 'autotune', r.get('autotune'))
+PY
+timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/r2c6_pytest.log 2>&1; echo "pytest exit $?"; tail -n 5 gpurun_out/r2c6_pytest.log
+timeout 600 python bench.py --steps 5 --warmup 3 > gpurun_out/r2c6_bench.json 2> gpurun_out/r2c6_bench.err; echo "bench exit $?"; tail -c 3000 gpurun_out/r2c6_bench.json; tail -n 3 gpurun_out/r2c6_bench.err

@@ -386,3 +386,52 @@ def test_build_all_fragments_shared_queue_largest_first(monkeypatch):
     assert order[0] == 6 and set(order[:2]) == {6, 3}  # largest fragments are handed out first
     with pytest.raises(ValueError):
         driver.FragmentERIBuilder(0, n_host_buffers=0)
+
+
+QUEUE_WORKER = r"""
+import os, sys, json, time
+sys.path.insert(0, sys.argv[1])
+import torch.distributed as dist
+from quemb_b200.driver import DistributedQueue
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+order = [7, 3, 5, 0, 1, 6, 2, 4, 8]
+got = {}
+for name in ("a", "b"):
+    q = DistributedQueue(dist, order, name)
+    mine = []
+    for i in q:
+        mine.append(i)
+        time.sleep(0.002 * (1 + 3 * rank))      # rank 1 is slower: it must end up with fewer fragments
+    got[name] = mine
+    assert q.taken == mine
+    dist.barrier()
+out = [None] * world
+dist.all_gather_object(out, got)
+if rank == 0:
+    print(json.dumps(out))
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_gloo_distributed_fragment_queue(tmp_path):
+    """Cross-rank dynamic hand-out (atomic counter in the process group's store): every fragment exactly once, in the
+    given order, the faster rank takes more; a second queue under another name starts from scratch."""
+    script = tmp_path / "queue_worker.py"
+    script.write_text(QUEUE_WORKER)
+    port = _free_port()
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(script), str(ROOT)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=240) for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    r0, r1 = json.loads(outs[0][0].strip().splitlines()[-1])
+    for name in ("a", "b"):
+        assert sorted(r0[name] + r1[name]) == list(range(9))
+        assert len(r0[name]) > len(r1[name])
+        merged = [7, 3, 5, 0, 1, 6, 2, 4, 8]
+        assert [i for i in merged if i in r0[name]] == r0[name]  # each rank sees its share in queue order

@@ -246,6 +246,34 @@ def test_background_writer_on_the_pinned_ring(q, tmp_path):
     b.close()
 
 
+def test_autotuned_output_mode_delivers_the_same_matrices(q):
+    """``Context.autotune_output`` balances PCIe against the host mirror threads; whatever split it picks, the
+    delivered (ij|kl) are the oracle's (every element arrives exactly once, by copy or by mirror)."""
+    from quemb_b200 import synthetic as syn
+    from quemb_b200.driver import FragmentERIBuilder
+
+    oracle = _oracle()
+    p = syn.sweep_point(100, 500, max_bytes=0.5e9)       # npair 5050: large enough for the column-group transfer
+    b = FragmentERIBuilder(0)
+    b.stage(p.unique_dense_data, (p.naux, p.nao, p.nao), p.exch_reachable, p.L_PQ, p.S_abs)
+    want = oracle.transform_integral(p.unique_dense_data, p.exch_reachable, p.TAs[-1], p.S_abs, p.L_PQ, p.MO_coeff_epsilon)
+    try:
+        tuned = b.tune_output()
+        assert tuned["d2h_gbs"] > 1.0 and tuned["mirror_gbs"] > 0.1 and 0.0 <= tuned["upper_fraction_over_pcie"] <= 1.0
+        for frac in (None, 0.0, 0.3, 0.7):
+            if frac is not None:
+                b.ctx.set_output_mode(True)
+                b.ctx.set_full_column_fraction(frac)
+            got = {}
+            b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: got.__setitem__(i, np.array(G)), indices=[len(p.TAs) - 1])
+            G = got[len(p.TAs) - 1]
+            assert np.abs(G - want).max() <= 1e-10 and np.array_equal(G, G.T), frac
+    finally:
+        b.ctx.set_output_mode(True)
+        b.ctx.set_full_column_fraction(0.0)
+        b.close()
+
+
 def test_n_host_buffers_is_clamped_to_the_ring_depth(q, caplog):
     from quemb_b200 import synthetic as syn
     from quemb_b200.driver import FragmentERIBuilder
