@@ -420,7 +420,12 @@ class SemiSparseSym3DTensor:
         flushes upload it again."""
         if self._dirty and self._host_mirror is not None:
             self._dirty = False
+            # a view handed out from a whitened tensor holds whitened values: writing them back must not turn the
+            # flag off (a full upload clears it)
+            was_whitened = self._has_device_data and self.whitened
             self.upload(self._host_mirror)
+            if was_whitened:
+                self.set_whitened(True)
 
     def _device_changed(self) -> None:
         """The device data were modified behind the host mirror (whiten, block staging, upload): the next access to
