@@ -79,6 +79,17 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, i
         "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
         : "memory");
 }
+// same, with an L2 eviction-priority hint (createpolicy): the row panels of the resident band of tiles are wanted
+// again by the next wave of CTAs (evict_last), the column panels stream through once per band (evict_first)
+__device__ __forceinline__ void tma_load_2d_hint(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar,
+                                                 uint64_t policy)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;"
+        ::"r"(smem_u32(dst)),
+        "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
 } // namespace
 
 struct GramTmaParams {
@@ -95,6 +106,7 @@ struct GramTmaParams {
     // 1: the lower tiles are ADDED (system-scope red.add.f64) into G, which may live in a peer GPU's memory (NVLink):
     // the reduce-sum of an aux-sharded fragment happens in the epilogue, tile by tile, while the other tiles compute
     int accumulate;
+    int hint; // L2 hints of the operand loads: 0 none, 1 row panel evict_last, 2 + column panel evict_first
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -122,6 +134,9 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == NCONSUMER_WARPS && lane == 0) {
             int s = 0, phase = 0;
+            uint64_t pol_last, pol_first;
+            asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
+            asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
             for (int w = blockIdx.x; w < p.ntiles * p.nsplit; w += gridDim.x) {
                 const int2 tt = p.tiles[w / p.nsplit];
                 const int m0 = tt.x * TM, n0 = tt.y * TN;
@@ -130,8 +145,14 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
                     mbar_wait(&empty[s], phase ^ 1);
                     mbar_expect_tx(&full[s], STAGE_BYTES);
                     uint8_t *As = smem + s * STAGE_BYTES;
-                    tma_load_2d(As, &tmap, kt * BK, m0, &full[s]);
-                    tma_load_2d(As + TILE_BYTES, &tmap, kt * BK, n0, &full[s]);
+                    if (p.hint >= 1)
+                        tma_load_2d_hint(As, &tmap, kt * BK, m0, &full[s], pol_last);
+                    else
+                        tma_load_2d(As, &tmap, kt * BK, m0, &full[s]);
+                    if (p.hint >= 2)
+                        tma_load_2d_hint(As + TILE_BYTES, &tmap, kt * BK, n0, &full[s], pol_first);
+                    else
+                        tma_load_2d(As + TILE_BYTES, &tmap, kt * BK, n0, &full[s]);
                     if (++s == STAGES) {
                         s = 0;
                         phase ^= 1;
@@ -313,7 +334,11 @@ cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
     cudaError_t e = cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
     const int nsplit = (p.partial && !p.accumulate) ? gram_splits(p.ntiles, p.ktiles, num_sms) : 1;
-    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles, 1, p.ktiles, 0, p.accumulate};
+    static const int hint = [] {
+        const char *e = std::getenv("QEMB_K3_HINT");
+        return e ? std::atoi(e) : 0;
+    }();
+    GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles, 1, p.ktiles, 0, p.accumulate, hint};
     if (nsplit > 1) {
         kp.G = p.partial;
         kp.ldg = p.npair;
