@@ -1,9 +1,13 @@
 // screen.cu -- MO->AO screening and small utility kernels.
 //
 // get_AO_per_MO (src/quemb/molbe/_cpp/eri_sparse_DF.cpp:443-465): X = |S_abs * TA|, keep X(mu,i) >= eps.
-// The sparsity pattern has to be bit-exact, so the sum over nu runs strictly left to right with
-// separately rounded multiply and add (__dmul_rn/__dadd_rn forbid FMA contraction): the same value the
-// plain-C oracle (and any non-fast-math scalar loop) produces.  Work is 2*nao^2*nmo flops -- tiny next
+// The sparsity pattern must match the reference's, so the sum over nu runs strictly left to right with
+// separately rounded multiply and add (__dmul_rn/__dadd_rn forbid FMA contraction): bit for bit the value the
+// plain-C oracle (and any non-fast-math scalar loop) produces.  The reference itself forms S_abs * TA with a blocked,
+// FMA, -ffast-math Eigen GEMM, i.e. in another summation order: an entry within rounding distance of eps can land on
+// the other side there.  Such entries are counted (bit 1 of the mask, qemb_fragment_borderline) and the driver logs
+// them; on every case of the test suite, full-size comparisons with the compiled reference included, the count is 0
+// and the lists are identical.  Work is 2*nao^2*nmo flops -- tiny next
 // to the contraction kernels -- so one thread per (mu, i) with coalesced S_abs reads is enough.
 #include "kernels.cuh"
 
