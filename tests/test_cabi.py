@@ -78,3 +78,22 @@ def test_host_mirror_lower(n):
     nt = ctypes.c_int()
     _lib.check(L.qemb_host_threads(ctypes.byref(nt)))
     assert nt.value >= 1
+
+
+def test_host_mirror_lower_avx2_path_in_a_fresh_process():
+    """The AVX2 mirror (hosts without AVX-512) is selected once per process: exercise it through QEMB_NO_AVX512."""
+    import os
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, ctypes, numpy as np; sys.path.insert(0, %r);"
+        "from quemb_b200 import _lib; L = _lib.lib();"
+        "rng = np.random.default_rng(0)\n"
+        "for n in (7, 300, 1030, 2051):\n"
+        "    G = np.asfortranarray(rng.standard_normal((n, n))); want = np.tril(G) + np.tril(G, -1).T\n"
+        "    assert L.qemb_host_mirror_lower(ctypes.c_void_p(G.ctypes.data), ctypes.c_int64(n), ctypes.c_int64(n)) == 0\n"
+        "    assert np.array_equal(G, want), n\n"
+        "print('ok')" % str(_lib.ROOT))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, QEMB_NO_AVX512="1"), capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "ok", r.stderr
