@@ -335,8 +335,10 @@ cudaError_t launch_gram(const GramParams &p, int num_sms, cudaStream_t s)
     if (e != cudaSuccess) return e;
     const int nsplit = (p.partial && !p.accumulate) ? gram_splits(p.ntiles, p.ktiles, num_sms) : 1;
     static const int hint = [] {
+        // default 1: row panels evict_last (8.10 instead of 8.48 GB of DRAM reads at npair 25425, same speed); hinting
+        // the column panels evict_first makes it worse (13 GB) -- profiles/k3_hint_r2.txt
         const char *e = std::getenv("QEMB_K3_HINT");
-        return e ? std::atoi(e) : 0;
+        return e ? std::atoi(e) : 1;
     }();
     GramTmaParams kp{p.ktiles, p.npair, p.G, p.ldg, p.tiles, p.ntiles, 1, p.ktiles, 0, p.accumulate, hint};
     if (nsplit > 1) {

@@ -97,3 +97,15 @@ def test_host_mirror_lower_avx2_path_in_a_fresh_process():
         "print('ok')" % str(_lib.ROOT))
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, QEMB_NO_AVX512="1"), capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.strip() == "ok", r.stderr
+
+
+def test_log_level_default_and_roundtrip_in_a_fresh_process():
+    """``get_log_level`` / ``set_log_level`` (``indexers.hpp:34-46``): process global, default Error = 40."""
+    import subprocess
+    import sys
+
+    code = ("import sys; sys.path.insert(0, %r); from quemb_b200 import eri_sparse_DF as q;"
+            "a = q.get_log_level(); q.set_log_level(20); b = q.get_log_level(); q.set_log_level(40); print(a, b, q.get_log_level())"
+            % str(_lib.ROOT))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.split() == ["40", "20", "40"], r.stderr

@@ -377,7 +377,8 @@ def test_info_level_prints_timer_lines(q, capfd):
     g = Golden("chain_small")
     T = q.SemiSparseSym3DTensor(g.M, (g.naux, g.nao, g.nao), g.exch)
     fr = g.frag(0)
-    assert q.get_log_level() == logging.ERROR  # the reference's default (hpp:34)
+    q.set_log_level(logging.ERROR)  # the reference's default (hpp:34; checked in a fresh process by test_cabi.py) --
+    # the seam forwards the root logger's level like the reference driver does (py:605), so it may differ by now
     q.transform_integral(T, fr["TA"], g.S_abs, g.L, g.eps)
     assert "[TIMER]" not in capfd.readouterr().out
     q.set_log_level(logging.INFO)
