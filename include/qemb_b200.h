@@ -244,6 +244,15 @@ int qemb_ctx_autotune_output(qemb_ctx *, double *d2h_gbs, double *mirror_gbs, do
  * QEMB_K3_INT8 or 0.  Applies to the accumulating transform (out_is_device == 2) as well: every slab is sliced with its
  * own exponents and its lower triangle added.  Slabs of more than 2^17 / slices rows stay on the FP64 path (int32). */
 int qemb_ctx_set_k3_int8_slices(qemb_ctx *ctx, int slices);
+/* Guaranteed-tolerance mode of the same opt-in variant (abs_tol > 0; 0 switches it off; overrides the fixed slice
+ * count): per fragment the largest column exponent e_max of X is reduced on the device first, and K3 runs with the
+ * smallest slice count S in 5 .. 8 whose WORST-CASE bound  qemb_k3_int8_bound(naux, S) * 2^(2 e_max)  is <= abs_tol for
+ * every (ij|kl) -- with the FP64 kernel when no S qualifies.  Costs one pass over X and a stream synchronisation per
+ * fragment.  qemb_fragment_k3_choice reports what the last K3 of a workspace ran with (slices 0 = FP64 kernel). */
+int qemb_ctx_set_k3_int8_tolerance(qemb_ctx *ctx, double abs_tol);
+/* worst case of |G_int8 - X^T X| per unit of 2^(e_i + e_j) for `slices` slices over `naux` auxiliary rows */
+int qemb_k3_int8_bound(int64_t naux, int slices, double *bound);
+int qemb_fragment_k3_choice(const qemb_workspace *, int *slices, int *max_expo);
 /* Host twin of the device slicer of the int8 K3 (same source: csrc/k3_int8_digits.h): exponent per column
  * (expo[c]; a column holding NaN / Inf gets the poison value -2^30 and zero digits) and the digits
  * D[(c * slices + a) * nrows + p].  Test hook for the CPU suite; no reference counterpart, not on the product path. */

@@ -123,6 +123,9 @@ _SIGS = {
     "qemb_ctx_set_output_mode": (c_int, [c_p, c_int]),
     "qemb_ctx_set_full_column_fraction": (c_int, [c_p, c_dbl]),
     "qemb_ctx_set_k3_int8_slices": (c_int, [c_p, c_int]),
+    "qemb_ctx_set_k3_int8_tolerance": (c_int, [c_p, c_dbl]),
+    "qemb_k3_int8_bound": (c_int, [c_i64, c_int, ctypes.POINTER(c_dbl)]),
+    "qemb_fragment_k3_choice": (c_int, [c_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "qemb_k3_int8_slice_host": (c_int, [c_p, c_i64, c_i64, c_i64, c_int, c_p, c_p]),
     "qemb_host_threads": (c_int, [ctypes.POINTER(c_int)]),
     "qemb_host_mirror_lower": (c_int, [c_p, c_i64, c_i64]),

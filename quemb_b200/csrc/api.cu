@@ -109,6 +109,9 @@ struct qemb_ctx {
     double full_frac = 0.0;
     // 0: K3 on the FP64 tensor path (default, the parity reference); 5 .. 8: opt-in int8-slice K3 (k3_int8.cu)
     int k3_slices = 0;
+    // > 0: guaranteed-tolerance mode of the int8-slice K3: per fragment the smallest slice count whose worst-case bound
+    // meets this ABSOLUTE tolerance on every (ij|kl), the FP64 kernel when none does (overrides k3_slices)
+    double k3_tol = 0.0;
     int num_sms = 148;
     std::atomic<int64_t> h2d_bytes{0}, d2h_bytes{0}; // bytes handed to the copy engines (uploads / G transfers)
     // every workspace runs its fragments on streams of its own (concurrent callers overlap on the device, small
@@ -369,6 +372,9 @@ struct qemb_workspace {
     // J/K consumer (jk.cu)
     DevBuf jk_in, jk_scratch, jk_out;
     DevBuf gram_i8; // scratch of the opt-in int8-slice K3
+    DevBuf k3_expo;       // device int: largest column exponent of X (guaranteed-tolerance mode)
+    HostBuf k3_expo_host; // its pinned landing place
+    int k3_last_slices = 0, k3_last_expo = 0; // what the last K3 of this workspace ran with (0 = FP64 kernel)
     cudaEvent_t jk_ev[2] = {nullptr, nullptr};
     float jk_ms = 0.f;
     HostBuf jk_stage[2];
@@ -534,6 +540,28 @@ extern "C" int qemb_ctx_set_k3_int8_slices(qemb_ctx *c, int slices)
 {
     REQ(c && (slices == 0 || (slices >= 5 && slices <= 8)), "slices must be 0 (FP64 K3) or 5 .. 8");
     c->k3_slices = slices;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_set_k3_int8_tolerance(qemb_ctx *c, double abs_tol)
+{
+    REQ(c && abs_tol >= 0.0 && abs_tol == abs_tol, "tolerance must be >= 0 (0 switches the mode off)");
+    c->k3_tol = abs_tol;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_k3_int8_bound(int64_t naux, int slices, double *bound)
+{
+    REQ(bound && naux >= 0 && slices >= 5 && slices <= 8, "bad argument");
+    *bound = gram_i8_bound(naux, slices);
+    return QEMB_OK;
+}
+
+extern "C" int qemb_fragment_k3_choice(const qemb_workspace *w, int *slices, int *max_expo)
+{
+    REQ(w && slices, "null argument");
+    *slices = w->k3_last_slices;
+    if (max_expo) *max_expo = w->k3_last_expo;
     return QEMB_OK;
 }
 
@@ -1315,6 +1343,8 @@ extern "C" void qemb_workspace_destroy(qemb_workspace *w)
     for (auto &e : w->jk_ev)
         if (e) cudaEventDestroy(e);
     w->gram_i8.release();
+    w->k3_expo.release();
+    w->k3_expo_host.release();
     for (int i = 0; i < 2; ++i) {
         w->jk_stage[i].release();
         if (w->jk_stage_free[i]) cudaEventDestroy(w->jk_stage_free[i]);
@@ -1811,7 +1841,26 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
     }
     // opt-in int8-slice K3 (k3_int8.cu), plain and accumulating; slabs deep enough to overflow the exact int32 sums stay
     // FP64 (digits in [-128, 127], at most `slices` digit pairs per order: slices * rows * 128^2 < 2^31)
-    if (w->ctx->k3_slices && (int64_t)w->ctx->k3_slices * w->mrows * 16384 < (int64_t)2147483647) {
+    int slices = w->ctx->k3_slices;
+    w->k3_last_expo = 0;
+    if (w->ctx->k3_tol > 0.0) {
+        // guaranteed-tolerance mode: e_max of X first (one pass over X, one int back: this waits for K2a, the price of
+        // deciding on the host which kernel instantiation runs), then the smallest S with bound * 2^(2 e_max) <= tol
+        TRY(w->k3_expo.reserve(sizeof(int)));
+        TRY(w->k3_expo_host.reserve(sizeof(int)));
+        CU(launch_max_expo(p.X, p.ldx, (int)w->mrows, s.npair, w->k3_expo.as<int>(), cs));
+        CU(cudaMemcpyAsync(w->k3_expo_host.p, w->k3_expo.p, sizeof(int), cudaMemcpyDeviceToHost, cs));
+        CU(cudaStreamSynchronize(cs));
+        w->ctx->launches += 1;
+        const int emax = *static_cast<int *>(w->k3_expo_host.p);
+        w->k3_last_expo = emax;
+        slices = 0;
+        for (int S = 5; S <= 8 && !slices; ++S)
+            if (emax <= -(1 << 29) || gram_i8_bound(w->mrows, S) * std::ldexp(1.0, 2 * emax) <= w->ctx->k3_tol) slices = S;
+    }
+    w->k3_last_slices = 0;
+    if (slices && (int64_t)slices * w->mrows * 16384 < (int64_t)2147483647) {
+        w->k3_last_slices = slices;
         GramI8Params q;
         q.X = p.X;
         q.ldx = p.ldx;
@@ -1819,7 +1868,7 @@ int gram(qemb_workspace *w, double *dst, int64_t ld, int accumulate = 0)
         q.npair = s.npair;
         q.G = dst;
         q.ldg = ld;
-        q.slices = w->ctx->k3_slices;
+        q.slices = slices;
         q.accumulate = accumulate;
         TRY(w->gram_i8.reserve(gram_i8_scratch_bytes(q.nrows, q.npair, q.slices)));
         q.scratch = w->gram_i8.as<int8_t>();

@@ -24,6 +24,8 @@
 #include "kernels.cuh"
 #include <cuda.h>
 
+#include <cmath>
+
 namespace qemb {
 
 namespace {
@@ -346,6 +348,62 @@ size_t gram_i8_scratch_bytes(int nrows, int64_t npair, int slices)
     const int64_t npair_pad = (npair + TM - 1) / TM * TM;
     const int64_t nI = npair_pad / TM;
     return (size_t)npair_pad * slices * gram_i8_naux_pad(nrows) + (size_t)npair_pad * 4 + (size_t)(nI * (nI + 1) + 2 * nI + 8) * sizeof(int2);
+}
+
+// ---- guaranteed-tolerance slice choice ------------------------------------------------------------------------
+// Largest binary exponent over the columns of X (frexp of the column maximum, the slicer's own rule; columns holding
+// a NaN / Inf or only zeros do not count).  With e_max known BEFORE slicing, gram_i8_bound(naux, S) * 2^(2 e_max) is a
+// worst-case bound on |G_int8 - X^T X| for every entry, so the smallest S that meets a caller tolerance can be picked
+// (and the FP64 kernel when none does).
+__global__ void max_expo_kernel(const double *X, int64_t ldx, int naux, int64_t npair, int *out)
+{
+    __shared__ double red[32];
+    for (int64_t j = blockIdx.x; j < npair; j += gridDim.x) {
+        const double *x = X + ldx * j;
+        double m = 0.0;
+        int bad = 0;
+        for (int p = threadIdx.x; p < naux; p += blockDim.x) {
+            const double a = fabs(x[p]);
+            m = fmax(m, a);
+            bad |= !(a <= 1.7976931348623157e308);
+        }
+        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+        bad = __syncthreads_or(bad);
+        if (threadIdx.x == 0) {
+            m = 0.0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) m = fmax(m, red[w]);
+            if (m > 0.0 && !bad) {
+                int e = 0;
+                frexp(m, &e);
+                atomicMax(out, e);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_max_expo(const double *X, int64_t ldx, int naux, int64_t npair, int *out_dev, cudaStream_t s)
+{
+    const int init = -(1 << 30);
+    cudaError_t e = cudaMemcpyAsync(out_dev, &init, sizeof(int), cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess || npair <= 0) return e;
+    max_expo_kernel<<<(unsigned)(npair < 148 * 8 ? npair : 148 * 8), 256, 0, s>>>(X, ldx, naux, npair, out_dev);
+    return cudaGetLastError();
+}
+
+// worst case of |G_int8 - X^T X| / 2^(e_i + e_j): remainders of both operands (|R| <= 2^-(8S-1) after rounding to
+// 8S-2 bits) plus the slice orders d >= S that are never formed (digits in [-128, 127]); oracle/k3_int8_oracle.py
+// `truncation_bound` is the same sum
+double gram_i8_bound(int64_t naux, int slices)
+{
+    const double rem = std::ldexp(1.0, -(8 * slices - 1));
+    double dropped = 0.0;
+    for (int d = slices; d < 2 * slices - 1; ++d) {
+        const int lo = d - slices + 1 > 0 ? d - slices + 1 : 0, hi = d < slices - 1 ? d : slices - 1;
+        dropped += (double)(hi - lo + 1) * 16384.0 * std::ldexp(1.0, -(8 * d + 12));
+    }
+    return (double)naux * (2.0 * rem * (1.0 + rem) + rem * rem + dropped);
 }
 
 cudaError_t launch_gram_int8(const GramI8Params &p, int num_sms, cudaStream_t s)

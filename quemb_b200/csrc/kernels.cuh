@@ -44,6 +44,10 @@ struct GramI8Params {
 int gram_i8_naux_pad(int nrows);
 size_t gram_i8_scratch_bytes(int nrows, int64_t npair, int slices);
 cudaError_t launch_gram_int8(const GramI8Params &p, int num_sms, cudaStream_t s);
+// guaranteed-tolerance mode: largest column exponent of X (device int, -2^30 when there is none) and the worst-case
+// bound of the S-slice product per unit of 2^(e_i + e_j)
+cudaError_t launch_max_expo(const double *X, int64_t ldx, int naux, int64_t npair, int *out_dev, cudaStream_t s);
+double gram_i8_bound(int64_t naux, int slices);
 
 // ---- K1 / K2a: grouped gather GEMM --------------------------------------------------------------
 //   C[:, ccol[n]] = sum_k  Asrc[:, acol[k]] * TA[brow[k], bcol[n]]        (k < K, n < N of the group)

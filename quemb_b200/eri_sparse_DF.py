@@ -100,6 +100,12 @@ class Context:
         ~ slices (slices + 1) / 2; see ``profiles/k3_int8_parity_study_r1.txt``)."""
         check(lib().qemb_ctx_set_k3_int8_slices(self._h, c_int(slices)))
 
+    def set_k3_int8_tolerance(self, abs_tol: float) -> None:
+        """Guaranteed-tolerance mode of the opt-in int8 K3 (``qemb_ctx_set_k3_int8_tolerance``): per fragment the
+        smallest slice count whose worst-case bound meets ``abs_tol`` on every (ij|kl), the FP64 kernel when none
+        does; 0 switches it off."""
+        check(lib().qemb_ctx_set_k3_int8_tolerance(self._h, c_dbl(abs_tol)))
+
     def set_timing(self, enabled: bool) -> None:
         check(lib().qemb_ctx_set_timing(self._h, c_int(1 if enabled else 0)))
 
@@ -141,6 +147,13 @@ def host_bandwidth(nbytes: int = 1 << 30) -> tuple[float, float]:
     w, c = c_dbl(), c_dbl()
     check(lib().qemb_host_bandwidth(c_i64(int(nbytes)), ctypes.byref(w), ctypes.byref(c)))
     return float(w.value), float(c.value)
+
+
+def k3_int8_bound(naux: int, slices: int) -> float:
+    """Worst case of ``|G_int8 - X^T X|`` per unit of ``2^(e_i + e_j)`` (``qemb_k3_int8_bound``)."""
+    b = c_dbl()
+    check(lib().qemb_k3_int8_bound(c_i64(naux), c_int(slices), ctypes.byref(b)))
+    return float(b.value)
 
 
 def output_ring_depth() -> int:
@@ -229,6 +242,13 @@ class Workspace:
         out = np.empty((npair, npair), order="F")
         check(lib().qemb_fragment_get_G(self._h, ptr(out), c_i64(npair)))
         return out
+
+    @property
+    def k3_choice(self) -> tuple[int, int]:
+        """(slices, max column exponent) the last K3 ran with; slices 0 = the FP64 kernel."""
+        a, b = c_int(), c_int()
+        check(lib().qemb_fragment_k3_choice(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     @property
     def borderline(self) -> int:

@@ -694,3 +694,45 @@ def test_k3_int8_accumulating_slabs(q, slices, tol):
     assert np.array_equal(G, G.T)
     assert np.abs(G - G64).max() <= tol * max(1.0, np.abs(G64).max())
     assert np.abs(G - G_oracle).max() <= TOL
+
+
+def test_k3_int8_guaranteed_tolerance_picks_the_smallest_sufficient_slice_count(q):
+    """Guaranteed-tolerance mode of the opt-in int8 K3: e_max of X is reduced on the device, the smallest S whose
+    worst-case bound meets the caller's absolute tolerance runs (the FP64 kernel when none does), and the result is
+    within that tolerance of the FP64 product -- on reference goldens."""
+    g = Golden("chain_small")
+    ctx = q.default_context(0)
+    T = q.SemiSparseSym3DTensor(g.M, (g.naux, g.nao, g.nao), g.exch, ctx=ctx)
+    L = q.GPU_MatrixHandle(g.L, ctx=ctx)
+    ws = q.Workspace(ctx)
+    fr = g.frag(0)
+    G64 = q.transform_integral(T, fr["TA"], g.S_abs, L, g.eps, ws=ws)
+    assert ws.k3_choice[0] == 0
+    # X of this fragment as the device holds it (solved in place) -> the exponent the device must find
+    from quemb_b200._lib import c_i64, check, lib, ptr
+
+    nmo = fr["TA"].shape[1]
+    X = np.empty((g.naux, nmo * (nmo + 1) // 2), order="F")
+    check(lib().qemb_fragment_get_sym(ws._h, ptr(X), c_i64(g.naux)))
+    m = np.abs(X).max(axis=0)
+    emax = int(np.frexp(m[m > 0].max())[1])
+    rows = -(-g.naux // 16) * 16
+    try:
+        seen = set()
+        for tol in (1e-30, 1e-13, 1e-11, 1e-9, 1e-6):
+            ctx.set_k3_int8_tolerance(tol)
+            G = q.transform_integral(T, fr["TA"], g.S_abs, L, g.eps, ws=ws)
+            S, e = ws.k3_choice
+            want = next((s for s in (5, 6, 7, 8) if q.k3_int8_bound(rows, s) * 2.0 ** (2 * emax) <= tol), 0)
+            assert e == emax and S == want, (tol, S, want, e, emax)
+            seen.add(S)
+            if S == 0:
+                assert np.array_equal(G, G64)
+            else:
+                assert np.abs(G - G64).max() <= tol + 1e-14 * np.abs(G64).max(), (tol, S)
+            assert np.abs(G - fr["G"]).max() <= max(1e-10, tol)
+        assert 0 in seen and len(seen) >= 3  # the tolerance actually steers the choice
+    finally:
+        ctx.set_k3_int8_tolerance(0.0)
+    G = q.transform_integral(T, fr["TA"], g.S_abs, L, g.eps, ws=ws)
+    assert ws.k3_choice[0] == 0 and np.array_equal(G, G64)

@@ -171,6 +171,21 @@ def test_consumer_oracle_two_independent_restatements_of_dot_eri_dm():
         assert abs(np.sum(D * vj) - Dp @ G @ Dp) <= 1e-11 * max(1.0, abs(Dp @ G @ Dp))
 
 
+def test_k3_int8_bound_of_the_library_is_the_restatements():
+    """The worst-case bound the guaranteed-tolerance mode decides with (``qemb_k3_int8_bound``) == the restatement's
+    ``truncation_bound``, term by term; and it orders the slice counts."""
+    from oracle import k3_int8_oracle as ko
+    from quemb_b200 import eri_sparse_DF as q
+
+    for naux in (1, 88, 700, 2716, 9024):
+        prev = None
+        for S in (5, 6, 7, 8):
+            b = q.k3_int8_bound(naux, S)
+            assert b == ko.truncation_bound(naux, S)
+            assert prev is None or b < prev / 100
+            prev = b
+
+
 def _int8_test_operand(rng, naux=300, npair=90):
     X = rng.standard_normal((naux, npair)) * np.exp(-6 * rng.random(npair))[None, :] * np.exp(-4 * rng.random(naux))[:, None]
     X[:, 7] = 0.0                                   # an all-zero pair
