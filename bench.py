@@ -609,6 +609,7 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
 
     # ---- cpu baseline (rank 0, N = 1 only): bounded sample of the reference's CPU path ------------------
     cpu_baseline = None
+    int8_extra = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         ref, kind, T_ref, works = reference_setup(p)
         small, large = int(np.argmin(works)), int(np.argmax(works))
@@ -621,6 +622,29 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
             got = {}
             b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: got.__setitem__(i, float(np.abs(G - G_ref).max())), indices=[f])
             parity[f] = got.get(f)
+            if f == large and not args.no_int8_extra:
+                # EXTRA, never the value (north star: all FP64): the opt-in int8-slice K3 in its guaranteed-tolerance
+                # mode (smallest slice count whose worst-case bound meets 1e-10 absolute on every (ij|kl), FP64 kernel
+                # otherwise), checked on the same full matrix of the largest fragment against the compiled reference
+                try:
+                    ctx.set_k3_int8_tolerance(args.int8_tolerance)
+                    got8 = {}
+                    b.build(p.TAs, p.MO_coeff_epsilon, lambda i, G: got8.__setitem__(i, float(np.abs(G - G_ref).max())), indices=[f])
+                    choice = b.ws.k3_choice
+                    ctx.synchronize()
+                    ctx.mark(6, "compute")
+                    for i in mine:
+                        b.build_device(p.TAs, p.MO_coeff_epsilon, Gdev.data_ptr(), indices=[i])
+                    ctx.mark(7, "compute")
+                    ctx.synchronize()
+                    int8_extra = {"mode": f"guaranteed tolerance {args.int8_tolerance:g} absolute (qemb_ctx_set_k3_int8_tolerance)",
+                                  "slices_chosen_largest_fragment": choice[0], "max_column_exponent": choice[1],
+                                  "parity_max_abs_vs_reference_largest_fragment": got8.get(f),
+                                  "all_fragments_device_s": ctx.mark_elapsed_ms(6, 7) * 1e-3,
+                                  "note": "metric application not included (the tensor is already whitened); compare with "
+                                          "`value` minus ~0.03 s"}
+                finally:
+                    ctx.set_k3_int8_tolerance(0.0)
             del G_ref
         serial = extrapolate_all_fragments(works, best)
         cpu_baseline = {
@@ -727,6 +751,7 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
                                  "matrices return to the host"},
         "e2e_file": e2e_file,
         "sharded": sharded,
+        "k3_int8_extra": int8_extra,
         "gpu_launches": launches_all,
         "clocks": clocks,
     }
@@ -841,6 +866,8 @@ def main() -> None:
     ap.add_argument("--file-dir", default=None)
     ap.add_argument("--file-fragments", type=int, default=2)
     ap.add_argument("--no-sharded-extra", action="store_true")
+    ap.add_argument("--no-int8-extra", action="store_true", help="skip the opt-in int8 K3 extra (N = 1, with the cpu baseline)")
+    ap.add_argument("--int8-tolerance", type=float, default=1e-10)
     ap.add_argument("--sharded-nmo", type=int, default=400)
     ap.add_argument("--sharded-naux", type=int, default=8000)
     ap.add_argument("--sharded-max-gb", type=float, default=6.0)
