@@ -229,12 +229,14 @@ int qemb_ctx_set_output_mode(qemb_ctx *, int mode);
  * pure triangle transfer) to the copy engine, which has slack while the kernels run. */
 int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
 
-/* Self-tuning of the two knobs above: measures this context's device -> host copy rate and the host threads' mirror
- * rate AT THE SAME TIME (call it on all ranks of a node at the same moment, e.g. right after a barrier) and sets the
- * output mode / full-column fraction so that PCIe and the host cores finish together: the fraction
- * (P - M) / (P + M) of the upper triangle crosses PCIe, the rest is mirrored.  Reports both rates (GB/s) and the
- * fraction (1.0 = the full square crosses PCIe, output mode 0). */
+/* Self-tuning of the two knobs above.  Measures on this context -- call it on all ranks of a node at the same moment,
+ * e.g. right after a barrier -- the device -> host copy rate with idle host threads (P0), the same rate while the host
+ * threads mirror a test matrix (P) and that mirror rate (M), and picks the cheaper of: full squares over PCIe
+ * (2U / P0), or the fraction f* = max(0, (P - M) / (P + M)) of the upper triangle over PCIe and the rest mirrored
+ * (max((1 + f) U / P, (1 - f) U / M)).  Reports P, M (GB/s) and the chosen fraction (1.0 = full squares, output mode
+ * 0); qemb_ctx_autotune_copy_alone returns P0. */
 int qemb_ctx_autotune_output(qemb_ctx *, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie);
+int qemb_ctx_autotune_copy_alone(const qemb_ctx *, double *d2h_alone_gbs);
 
 /* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 5 .. 8 = error-free
  * split of X into that many 8-bit integer slices (balanced base-256 digits of each column rounded below its exponent)

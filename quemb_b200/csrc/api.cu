@@ -112,6 +112,7 @@ struct qemb_ctx {
     // > 0: guaranteed-tolerance mode of the int8-slice K3: per fragment the smallest slice count whose worst-case bound
     // meets this ABSOLUTE tolerance on every (ij|kl), the FP64 kernel when none does (overrides k3_slices)
     double k3_tol = 0.0;
+    double tune_p0 = 0.0; // device -> host rate with idle host threads, last autotune
     int num_sms = 148;
     std::atomic<int64_t> h2d_bytes{0}, d2h_bytes{0}; // bytes handed to the copy engines (uploads / G transfers)
     // every workspace runs its fragments on streams of its own (concurrent callers overlap on the device, small
@@ -677,13 +678,16 @@ extern "C" int qemb_host_bandwidth(int64_t bytes, double *write_gbs, double *cop
     return QEMB_OK;
 }
 
-// Self-tuning of how a host-bound (ij|kl) travels (output mode 1 + full-column fraction): times a device -> host copy
-// into pinned memory on the copy stream WHILE the library's host threads mirror a test matrix, i.e. both rates under
-// the contention they will see in a build (other ranks of the node calling this at the same moment included), and
-// balances the two: with P = copy rate and M = mirror rate (bytes of upper triangle produced per second), sending the
-// fraction f = (P - M) / (P + M) of the upper triangle over PCIe and mirroring the rest makes both finish together
-// (lower triangle ~ upper triangle ~ U bytes: (U + f U) / P = (1 - f) U / M).  f <= 0: pure triangle transfer;
-// f >= 0.9: the full square crosses PCIe and no CPU pass is made.
+// Self-tuning of how a host-bound (ij|kl) travels (output mode + full-column fraction).  Three rates are measured on
+// this context, all ranks of a node calling at the same moment so that the contention is the real one:
+//   P0  device -> host copy into pinned memory with the host threads idle      (what a full-square transfer gets)
+//   P   the same copy WHILE the library's host threads mirror a test matrix    (what a triangle transfer gets)
+//   M   the mirror rate during that time (bytes of upper triangle produced per second)
+// With L ~ U bytes of lower / upper triangle:  full squares take 2U / P0;  sending the fraction f of the upper triangle
+// over PCIe and mirroring the rest takes max((1 + f) U / P, (1 - f) U / M), least at f* = max(0, (P - M) / (P + M)).
+// The cheaper of the two is chosen (the copy engine loses up to half its rate to the mirror's DRAM traffic on some
+// hosts, so neither extreme wins everywhere: N = 1 boxes want the pure triangle, the 2-GPU box full squares, four
+// GPUs behind one PCIe switch a split).
 extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie)
 {
     REQ(c != nullptr, "null ctx");
@@ -692,48 +696,65 @@ extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mi
     const size_t mbytes = (size_t)n * n * 8, cbytes = 256u << 20;
     const int ncopies = 6;
     void *hm = nullptr, *hc = nullptr, *dv = nullptr;
-    cudaError_t e = cudaMallocHost(&hm, mbytes);
-    if (e == cudaSuccess) e = cudaMallocHost(&hc, cbytes);
-    if (e == cudaSuccess) e = cudaMalloc(&dv, cbytes);
-    if (e != cudaSuccess) {
-        (void)cudaGetLastError();
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    auto cleanup = [&] {
+        for (auto &e : ev)
+            if (e) cudaEventDestroy(e);
         if (hm) cudaFreeHost(hm);
         if (hc) cudaFreeHost(hc);
         if (dv) cudaFree(dv);
+    };
+    cudaError_t e = cudaMallocHost(&hm, mbytes);
+    if (e == cudaSuccess) e = cudaMallocHost(&hc, cbytes);
+    if (e == cudaSuccess) e = cudaMalloc(&dv, cbytes);
+    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&ev[i]);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        cleanup();
         return fail(QEMB_ENOMEM, std::string("autotune buffers: ") + cudaGetErrorString(e));
     }
     std::memset(hm, 0, mbytes);
-    cudaEvent_t e0, e1;
-    CU(cudaEventCreate(&e0));
-    CU(cudaEventCreate(&e1));
-    CU(cudaMemsetAsync(dv, 0, cbytes, c->copy));
-    CU(cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy)); // warm-up
-    CU(cudaStreamSynchronize(c->copy));
-    qemb_host_mirror_lower(static_cast<double *>(hm), n, 1024);             // warm-up (threads, page faults)
-    CU(cudaEventRecord(e0, c->copy));
-    for (int i = 0; i < ncopies; ++i) CU(cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy));
-    CU(cudaEventRecord(e1, c->copy));
-    const auto t0 = std::chrono::steady_clock::now();
     int reps = 0;
-    do {  // keep the host threads mirroring for as long as the copies run
-        qemb_host_mirror_lower(static_cast<double *>(hm), n, n);
-        ++reps;
-    } while (cudaEventQuery(e1) == cudaErrorNotReady && reps < 64);
-    const double tm = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    (void)cudaGetLastError();
-    CU(cudaEventSynchronize(e1));
-    float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    cudaFreeHost(hm);
-    cudaFreeHost(hc);
-    cudaFree(dv);
-    const double P = (double)ncopies * (double)cbytes / (ms * 1e-3) / 1e9;
+    double tm = 0.0;
+    float ms0 = 0.f, ms1 = 0.f;
+    auto run = [&]() -> cudaError_t {
+        cudaError_t r = cudaMemsetAsync(dv, 0, cbytes, c->copy);
+        if (r == cudaSuccess) r = cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy); // warm-up
+        if (r == cudaSuccess) r = cudaStreamSynchronize(c->copy);
+        if (r != cudaSuccess) return r;
+        qemb_host_mirror_lower(static_cast<double *>(hm), n, 1024); // warm-up (threads, page faults)
+        // phase 1: the copy engine alone
+        r = cudaEventRecord(ev[0], c->copy);
+        for (int i = 0; i < ncopies && r == cudaSuccess; ++i) r = cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy);
+        if (r == cudaSuccess) r = cudaEventRecord(ev[1], c->copy);
+        if (r == cudaSuccess) r = cudaEventSynchronize(ev[1]);
+        // phase 2: the same copies while the host threads mirror
+        if (r == cudaSuccess) r = cudaEventRecord(ev[2], c->copy);
+        for (int i = 0; i < ncopies && r == cudaSuccess; ++i) r = cudaMemcpyAsync(hc, dv, cbytes, cudaMemcpyDeviceToHost, c->copy);
+        if (r == cudaSuccess) r = cudaEventRecord(ev[3], c->copy);
+        if (r != cudaSuccess) return r;
+        const auto t0 = std::chrono::steady_clock::now();
+        do {
+            qemb_host_mirror_lower(static_cast<double *>(hm), n, n);
+            ++reps;
+        } while (cudaEventQuery(ev[3]) == cudaErrorNotReady && reps < 64);
+        tm = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        (void)cudaGetLastError();
+        r = cudaEventSynchronize(ev[3]);
+        if (r == cudaSuccess) r = cudaEventElapsedTime(&ms0, ev[0], ev[1]);
+        if (r == cudaSuccess) r = cudaEventElapsedTime(&ms1, ev[2], ev[3]);
+        return r;
+    };
+    e = run();
+    cleanup();
+    if (e != cudaSuccess) return fail(QEMB_ECUDA, std::string("autotune: ") + cudaGetErrorString(e));
+    const double bytes = (double)ncopies * (double)cbytes;
+    const double P0 = bytes / (ms0 * 1e-3) / 1e9, P = bytes / (ms1 * 1e-3) / 1e9;
     const double M = (double)reps * (double)n * (double)(n - 1) / 2.0 * 8.0 / tm / 1e9;
     double f = (P - M) / (P + M);
     f = f < 0.0 ? 0.0 : f;
-    if (f >= 0.9) {
+    const double t_split = std::max((1.0 + f) / P, (1.0 - f) / M), t_full = 2.0 / P0; // per byte of U
+    if (f >= 0.9 || t_full <= t_split) {
         c->out_mode = 0;
         c->full_frac = 0.0;
         f = 1.0;
@@ -741,9 +762,18 @@ extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mi
         c->out_mode = 1;
         c->full_frac = 1.0 - std::sqrt(1.0 - f); // whole columns [cs, n) carry 1 - (cs / n)^2 of the upper triangle
     }
+    c->tune_p0 = P0;
     if (d2h_gbs) *d2h_gbs = P;
     if (mirror_gbs) *mirror_gbs = M;
     if (upper_fraction_pcie) *upper_fraction_pcie = f;
+    return QEMB_OK;
+}
+
+// copy rate with the host threads idle, from the last qemb_ctx_autotune_output (GB/s; 0 before the first call)
+extern "C" int qemb_ctx_autotune_copy_alone(const qemb_ctx *c, double *d2h_alone_gbs)
+{
+    REQ(c && d2h_alone_gbs, "null argument");
+    *d2h_alone_gbs = c->tune_p0;
     return QEMB_OK;
 }
 

@@ -87,12 +87,14 @@ class Context:
         check(lib().qemb_ctx_set_full_column_fraction(self._h, c_dbl(frac)))
 
     def autotune_output(self) -> dict[str, float]:
-        """Measure this context's device->host copy rate and the host threads' mirror rate under mutual contention
-        and set output mode / full-column fraction so that both finish together (``qemb_ctx_autotune_output``).
+        """Measure this context's device->host copy rate alone and under the host mirror's contention plus the mirror
+        rate, and set output mode / full-column fraction to the cheaper of full squares and a balanced split
+        (``qemb_ctx_autotune_output``).
         With several ranks per node call it on all of them at the same moment (after a barrier)."""
-        p, m, f = c_dbl(), c_dbl(), c_dbl()
+        p, m, f, p0 = c_dbl(), c_dbl(), c_dbl(), c_dbl()
         check(lib().qemb_ctx_autotune_output(self._h, ctypes.byref(p), ctypes.byref(m), ctypes.byref(f)))
-        return {"d2h_gbs": p.value, "mirror_gbs": m.value, "upper_fraction_over_pcie": f.value}
+        check(lib().qemb_ctx_autotune_copy_alone(self._h, ctypes.byref(p0)))
+        return {"d2h_alone_gbs": p0.value, "d2h_gbs": p.value, "mirror_gbs": m.value, "upper_fraction_over_pcie": f.value}
 
     def set_k3_int8_slices(self, slices: int) -> None:
         """Opt-in K3 on the int8 tensor cores (0 = FP64 path, the default and the parity reference; 5 .. 8 integer
