@@ -38,7 +38,6 @@ import json  # noqa: E402
 import shutil  # noqa: E402
 import subprocess  # noqa: E402
 import tempfile  # noqa: E402
-import threading  # noqa: E402
 import time  # noqa: E402
 from pathlib import Path  # noqa: E402
 
@@ -455,7 +454,7 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
                            "fragment_nmo": int(n_last), "ms": best, "gbs": nb / best / 1e6}
 
     # ---- e2e: host buffers in, pinned host buffers out ------------------------------------------------
-    result_bytes = sum(8 * (t.shape[1] * (t.shape[1] + 1) // 2) ** 2 for t in (p.TAs[i] for i in mine))
+
     # How a host-bound (ij|kl) travels: the lower triangle always crosses PCIe; of the upper triangle a fraction crosses
     # PCIe as well and the rest is rebuilt by the library's host threads.  "auto": every rank measures its own copy
     # rate and mirror rate at the same moment (all ranks, mutual contention included) and balances the two
