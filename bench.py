@@ -462,7 +462,12 @@ def run_b200(args, rank: int, world: int, local_rank: int) -> None:
     out_mode = args.e2e_output
     barrier()
     if out_mode == "auto":
-        tuned = b.tune_output()
+        try:
+            tuned = b.tune_output()
+        except Exception as e:  # noqa: BLE001  -- tuning must never take the measurement down: fall back to a fixed mode
+            ctx.set_output_mode(world == 1)
+            ctx.set_full_column_fraction(0.0)
+            tuned = {"error": f"{type(e).__name__}: {e}", "upper_fraction_over_pcie": 0.0 if world == 1 else 1.0}
     else:
         ctx.set_output_mode(out_mode == "triangle")
         ctx.set_full_column_fraction(0.0)

@@ -237,6 +237,10 @@ int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
  * 0); qemb_ctx_autotune_copy_alone returns P0. */
 int qemb_ctx_autotune_output(qemb_ctx *, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie);
 int qemb_ctx_autotune_copy_alone(const qemb_ctx *, double *d2h_alone_gbs);
+/* The model only proposes: qemb_ctx_autotune_output then RUNS the candidates -- full squares, pure triangle, the model's
+ * split -- as four back-to-back deliveries of a 0.5 GB test matrix each through the real output path and keeps the
+ * fastest (the model's choice stands if the trials cannot run).  Seconds per candidate, -1 = not run: */
+int qemb_ctx_autotune_trials(const qemb_ctx *, double *secs3);
 
 /* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 5 .. 8 = error-free
  * split of X into that many 8-bit integer slices (balanced base-256 digits of each column rounded below its exponent)

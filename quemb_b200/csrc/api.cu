@@ -113,6 +113,7 @@ struct qemb_ctx {
     // meets this ABSOLUTE tolerance on every (ij|kl), the FP64 kernel when none does (overrides k3_slices)
     double k3_tol = 0.0;
     double tune_p0 = 0.0; // device -> host rate with idle host threads, last autotune
+    double tune_secs[3] = {-1.0, -1.0, -1.0}; // trial deliveries of the last autotune: full squares, triangle, model split
     int num_sms = 148;
     std::atomic<int64_t> h2d_bytes{0}, d2h_bytes{0}; // bytes handed to the copy engines (uploads / G transfers)
     // every workspace runs its fragments on streams of its own (concurrent callers overlap on the device, small
@@ -688,13 +689,13 @@ extern "C" int qemb_host_bandwidth(int64_t bytes, double *write_gbs, double *cop
 // The cheaper of the two is chosen (the copy engine loses up to half its rate to the mirror's DRAM traffic on some
 // hosts, so neither extreme wins everywhere: N = 1 boxes want the pure triangle, the 2-GPU box full squares, four
 // GPUs behind one PCIe switch a split).
-extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie)
+static int autotune_model(qemb_ctx *c, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie)
 {
     REQ(c != nullptr, "null ctx");
     DeviceGuard g(c->device);
     const int64_t n = 6144;                       // mirror test matrix: 6144^2 doubles = 302 MB
     const size_t mbytes = (size_t)n * n * 8, cbytes = 256u << 20;
-    const int ncopies = 6;
+    const int ncopies = 8;
     void *hm = nullptr, *hc = nullptr, *dv = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     auto cleanup = [&] {
@@ -2408,6 +2409,101 @@ extern "C" int qemb_device_to_host(qemb_ctx *c, void *host, const void *dev, int
     CU(cudaMemcpyAsync(host, dev, (size_t)bytes, cudaMemcpyDefault, c->compute)); // UVA: `host` may be any pointer
     c->d2h_bytes += bytes;
     CU(cudaStreamSynchronize(c->compute));
+    return QEMB_OK;
+}
+
+// Self-tuning, second stage: the model of autotune_model picks a split f*, but the rates it rests on move with the
+// contention of a real delivery (the copy engine loses more to the mirror's DRAM traffic in a build than in a short
+// probe; measured on the 2-GPU box: model 1.29 U / 42.5 GB/s, build 32 GB/s).  So the candidates -- full squares, the
+// pure triangle, the split f* -- are RUN: a test matrix of n x n doubles is delivered `reps` times back to back through
+// the real machinery (column groups on the copy stream, completion callbacks, mirror tasks on the host pool, two host
+// buffers in rotation) and the fastest wins.  All ranks of a node call this at the same moment and walk the candidates
+// in the same order, so every candidate is timed under the contention it would see.
+extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie)
+{
+    double P = 0, M = 0, f = 0;
+    TRY(autotune_model(c, &P, &M, &f));
+    if (d2h_gbs) *d2h_gbs = P;
+    if (mirror_gbs) *mirror_gbs = M;
+    if (upper_fraction_pcie) *upper_fraction_pcie = f; // the model's choice stands unless the trials below complete
+    DeviceGuard g(c->device);
+    const int model_mode = c->out_mode;
+    const double model_frac = c->full_frac;
+    const int64_t n = 8192; // 0.5 GB per delivery
+    const int reps = 4;
+    const size_t bytes = (size_t)n * n * 8;
+    struct Cand {
+        int mode;
+        double frac, upper, secs;
+    } cand[3] = {{0, 0.0, 1.0, -1.0}, {1, 0.0, 0.0, -1.0}, {1, 0.0, f, -1.0}};
+    int ncand = 2;
+    if (f > 0.03 && f < 0.9) {
+        cand[2].frac = 1.0 - std::sqrt(1.0 - f);
+        ncand = 3;
+    }
+    for (int k = 0; k < 3; ++k) c->tune_secs[k] = -1.0;
+    qemb_workspace *w = nullptr;
+    void *dv = nullptr, *hb[2] = {nullptr, nullptr};
+    auto cleanup = [&] {
+        if (w) qemb_workspace_destroy(w);
+        if (dv) cudaFree(dv);
+        for (auto &h : hb)
+            if (h) cudaFreeHost(h);
+    };
+    const int rc = qemb_workspace_create(c, &w);
+    cudaError_t e = rc == QEMB_OK ? cudaMalloc(&dv, bytes) : cudaErrorUnknown;
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaMallocHost(&hb[i], bytes);
+    if (e == cudaSuccess) e = cudaMemsetAsync(dv, 0, bytes, c->copy);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->copy);
+    if (rc != QEMB_OK || e != cudaSuccess) {
+        (void)cudaGetLastError();
+        cleanup();
+        return QEMB_OK;
+    }
+    for (int k = 0; k < ncand; ++k) {
+        c->out_mode = cand[k].mode;
+        c->full_frac = cand[k].frac;
+        bool ok = true;
+        std::chrono::steady_clock::time_point t0;
+        for (int r = 0; r < reps + 1 && ok; ++r) { // the first delivery warms the path up and is not timed
+            if (r == 1) {
+                ok = qemb_fragment_wait_output(w, w->ticket) == QEMB_OK;
+                t0 = std::chrono::steady_clock::now();
+            }
+            if (r >= 3) ok = ok && qemb_fragment_wait_output(w, w->ticket - 1) == QEMB_OK; // host buffer r & 1 is free again
+            w->ticket += 1;
+            OutJob &job = w->jobs[w->ticket % OUT_RING];
+            wait_job(job);
+            ok = ok && send_G(w, job, static_cast<double *>(dv), n, static_cast<double *>(hb[r & 1]), n) == QEMB_OK;
+            ok = ok && cudaEventRecord(w->out_done[w->ticket % OUT_RING], c->copy) == cudaSuccess;
+        }
+        ok = ok && qemb_fragment_wait_output(w, w->ticket - 1) == QEMB_OK && qemb_fragment_wait_output(w, w->ticket) == QEMB_OK;
+        if (ok) cand[k].secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        qemb_ctx_synchronize(c);
+    }
+    int best = -1;
+    for (int k = 0; k < ncand; ++k)
+        if (cand[k].secs > 0 && (best < 0 || cand[k].secs < cand[best].secs)) best = k;
+    cleanup();
+    if (best < 0) { // nothing could be timed: keep the model's choice
+        (void)cudaGetLastError();
+        c->out_mode = model_mode;
+        c->full_frac = model_frac;
+        return QEMB_OK;
+    }
+    c->out_mode = cand[best].mode;
+    c->full_frac = cand[best].frac;
+    for (int k = 0; k < ncand; ++k) c->tune_secs[k] = cand[k].secs;
+    if (upper_fraction_pcie) *upper_fraction_pcie = cand[best].upper;
+    return QEMB_OK;
+}
+
+// seconds the candidates of the last qemb_ctx_autotune_output took for their test deliveries (4 x 0.5 GB): full
+// squares, pure triangle, model split (-1: not run)
+extern "C" int qemb_ctx_autotune_trials(const qemb_ctx *c, double *secs3)
+{
+    REQ(c && secs3, "null argument");
+    for (int k = 0; k < 3; ++k) secs3[k] = c->tune_secs[k];
     return QEMB_OK;
 }
 

@@ -94,7 +94,10 @@ class Context:
         p, m, f, p0 = c_dbl(), c_dbl(), c_dbl(), c_dbl()
         check(lib().qemb_ctx_autotune_output(self._h, ctypes.byref(p), ctypes.byref(m), ctypes.byref(f)))
         check(lib().qemb_ctx_autotune_copy_alone(self._h, ctypes.byref(p0)))
-        return {"d2h_alone_gbs": p0.value, "d2h_gbs": p.value, "mirror_gbs": m.value, "upper_fraction_over_pcie": f.value}
+        t = (c_dbl * 3)()
+        check(lib().qemb_ctx_autotune_trials(self._h, t))
+        return {"d2h_alone_gbs": p0.value, "d2h_gbs": p.value, "mirror_gbs": m.value, "upper_fraction_over_pcie": f.value,
+                "trial_s_full_triangle_split": [float(x) for x in t]}
 
     def set_k3_int8_slices(self, slices: int) -> None:
         """Opt-in K3 on the int8 tensor cores (0 = FP64 path, the default and the parity reference; 5 .. 8 integer
