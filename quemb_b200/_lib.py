@@ -124,6 +124,7 @@ _SIGS = {
     "qemb_ctx_set_timing": (c_int, [c_p, c_int]),
     "qemb_ctx_set_output_mode": (c_int, [c_p, c_int]),
     "qemb_ctx_set_full_column_fraction": (c_int, [c_p, c_dbl]),
+    "qemb_ctx_set_output_group_bytes": (c_int, [c_p, c_i64]),
     "qemb_ctx_set_k3_int8_slices": (c_int, [c_p, c_int]),
     "qemb_ctx_set_k3_int8_tolerance": (c_int, [c_p, c_dbl]),
     "qemb_k3_int8_bound": (c_int, [c_i64, c_int, ctypes.POINTER(c_dbl)]),

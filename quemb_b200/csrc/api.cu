@@ -107,6 +107,8 @@ struct qemb_ctx {
     // mode 1 only: the last `full_frac` of the columns cross PCIe whole (rows 0..n) and are not mirrored on the host:
     // balances the copy engine (slack) against the host threads (the bottleneck of a pure triangle transfer)
     double full_frac = 0.0;
+    // bytes per copy group of a triangle transfer: the host starts mirroring a group as soon as it has landed
+    int64_t out_group_bytes = 64ll << 20;
     // 0: K3 on the FP64 tensor path (default, the parity reference); 5 .. 8: opt-in int8-slice K3 (k3_int8.cu)
     int k3_slices = 0;
     // > 0: guaranteed-tolerance mode of the int8-slice K3: per fragment the smallest slice count whose worst-case bound
@@ -528,6 +530,13 @@ extern "C" int qemb_ctx_set_output_mode(qemb_ctx *c, int mode)
     REQ(c != nullptr, "null ctx");
     REQ(mode == 0 || mode == 1, "output mode must be 0 (full square over PCIe) or 1 (lower triangle + host mirror)");
     c->out_mode = mode;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_ctx_set_output_group_bytes(qemb_ctx *c, int64_t bytes)
+{
+    REQ(c && bytes >= (1 << 20) && bytes <= (1ll << 32), "group size must be between 1 MB and 4 GB");
+    c->out_group_bytes = bytes;
     return QEMB_OK;
 }
 
@@ -2079,7 +2088,7 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         std::lock_guard<std::mutex> lk2(w->ctx->out_mutex);
         w->ctx->out_pending += 1;
     }
-    const int64_t target = 64ll << 20;
+    const int64_t target = w->ctx->out_group_bytes;
     // column split: [0, csplit) travel as lower triangle + host mirror, [csplit, n) whole
     int64_t csplit = n;
     if (w->ctx->full_frac > 0.0) csplit = std::max<int64_t>(0, (int64_t)((1.0 - w->ctx->full_frac) * (double)n) / 256 * 256);

@@ -86,6 +86,10 @@ class Context:
         by the host threads."""
         check(lib().qemb_ctx_set_full_column_fraction(self._h, c_dbl(frac)))
 
+    def set_output_group_bytes(self, nbytes: int) -> None:
+        """Triangle output mode: bytes per copy group (the host mirrors a group once it has landed; default 64 MB)."""
+        check(lib().qemb_ctx_set_output_group_bytes(self._h, c_i64(int(nbytes))))
+
     def autotune_output(self) -> dict[str, float]:
         """Measure this context's device->host copy rate alone and under the host mirror's contention plus the mirror
         rate, and set output mode / full-column fraction to the cheaper of full squares and a balanced split
