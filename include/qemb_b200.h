@@ -228,7 +228,7 @@ int qemb_ctx_set_output_mode(qemb_ctx *, int mode);
  * the host threads (default: QEMB_FULL_COLUMN_FRACTION or 0).  Shifts work from the host cores (the bottleneck of the
  * pure triangle transfer) to the copy engine, which has slack while the kernels run. */
 int qemb_ctx_set_full_column_fraction(qemb_ctx *, double frac);
-/* Output mode 1 only: bytes per column group of the triangle transfer (default 64 MB).  The host threads start
+/* Output mode 1 only: bytes per column group of the triangle transfer (default 256 MB).  The host threads start
  * mirroring a group when its copy has completed; smaller groups start earlier and may still find the data in the
  * last-level cache, larger ones amortise the per-copy overhead. */
 int qemb_ctx_set_output_group_bytes(qemb_ctx *, int64_t bytes);

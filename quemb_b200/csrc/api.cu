@@ -108,7 +108,7 @@ struct qemb_ctx {
     // balances the copy engine (slack) against the host threads (the bottleneck of a pure triangle transfer)
     double full_frac = 0.0;
     // bytes per copy group of a triangle transfer: the host starts mirroring a group as soon as it has landed
-    int64_t out_group_bytes = 64ll << 20;
+    int64_t out_group_bytes = 256ll << 20; // measured at N = 1 (profiles/e2e_group_size_r2_n1.txt): 8 MB 2.78 s ... 64 MB 1.95 s, 256 MB 1.85 s per build
     // 0: K3 on the FP64 tensor path (default, the parity reference); 5 .. 8: opt-in int8-slice K3 (k3_int8.cu)
     int k3_slices = 0;
     // > 0: guaranteed-tolerance mode of the int8-slice K3: per fragment the smallest slice count whose worst-case bound

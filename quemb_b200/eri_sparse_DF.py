@@ -87,7 +87,7 @@ class Context:
         check(lib().qemb_ctx_set_full_column_fraction(self._h, c_dbl(frac)))
 
     def set_output_group_bytes(self, nbytes: int) -> None:
-        """Triangle output mode: bytes per copy group (the host mirrors a group once it has landed; default 64 MB)."""
+        """Triangle output mode: bytes per copy group (the host mirrors a group once it has landed; default 256 MB)."""
         check(lib().qemb_ctx_set_output_group_bytes(self._h, c_i64(int(nbytes))))
 
     def autotune_output(self) -> dict[str, float]:

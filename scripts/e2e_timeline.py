@@ -91,7 +91,7 @@ def main():
             kind, frac = fields[0], (fields[1] if len(fields) > 1 else "")
             ctx.set_output_mode(kind == "triangle")
             ctx.set_full_column_fraction(float(frac) if frac else 0.0)
-            ctx.set_output_group_bytes(int(float(fields[2]) * (1 << 20)) if len(fields) > 2 else 64 << 20)
+            ctx.set_output_group_bytes(int(float(fields[2]) * (1 << 20)) if len(fields) > 2 else 256 << 20)
         order_all = sorted(range(len(p.TAs)), key=lambda i: (-costs[i], i))
         rows = []
         for rep in range(args.reps + 1):
