@@ -863,8 +863,8 @@ def main() -> None:
     ap.add_argument("--workload", default="c32h66", choices=["c32h66", "octane", "tiny"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-output", default="auto", choices=["auto", "triangle", "full"],
-                    help="how a host-bound (ij|kl) travels: lower triangle + host mirror, or the full square (auto: "
-                         "triangle on 1 GPU, full square on several)")
+                    help="how a host-bound (ij|kl) travels: lower triangle + host mirror, the full square, or (auto, default) "
+                         "whatever the library's self-tuning measures to be fastest on this host, per rank")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (default: --steps)")
     ap.add_argument("--no-file", action="store_true", help="skip the bounded delivery-to-file sample")
     ap.add_argument("--file-dir", default=None)

@@ -2077,7 +2077,7 @@ int send_G(qemb_workspace *w, OutJob &job, const double *G, int64_t n, double *o
         CU(cudaMemcpy2DAsync(out, (size_t)ld_out * 8, G, (size_t)n * 8, (size_t)n * 8, (size_t)n, cudaMemcpyDeviceToHost, cs));
         return QEMB_OK;
     }
-    // column groups of ~64 MB; group [c0, c1) sends rows [c0, n) (its diagonal block travels whole), the
+    // column groups of ~out_group_bytes; group [c0, c1) sends rows [c0, n) (its diagonal block travels whole), the
     // host mirrors rows [c1, n) of it into G[c0:c1, c1:n] as soon as the group has landed
     {
         std::lock_guard<std::mutex> lk(job.m);
