@@ -310,6 +310,27 @@ int qemb_host_free(void *p);
  * the cuBLAS figure). */
 int qemb_probe_dmma_tflops(qemb_ctx *, int64_t n, int64_t k, int iters, double *tflops);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * K3 for one small fragment, G = X^T X (what qemb_fragment_gram computes, cpp:620), with NO allocation of any kind:
+ * the split-K partial matrices live in a file-scope `static __device__` array of 32 MiB (csrc/gram_noalloc.cu; every
+ * GPU that loads that module holds it until the process exits), whose device address is taken once per device with
+ * cudaGetSymbolAddress.  The caller passes input and output:
+ *   X_dev   naux x npair FP64, column-major, leading dimension ldx >= naux, ldx even, 16-byte aligned (TMA); rows
+ *           [naux, ldx) are never read, so no zero padding is needed
+ *   G_dev   npair x npair FP64 (both triangles written), leading dimension ldg >= npair
+ *   stream  cudaStream_t as void* (NULL = default stream) of the CURRENT device, which must own X_dev and G_dev;
+ *           asynchronous: two kernel launches are enqueued, nothing is synchronised.
+ * Limit: npair <= 2048 (qemb_gram_noalloc_limits reports it and the array size); larger sizes fail with QEMB_EINVAL
+ * and a message naming the limit -- use qemb_fragment_gram / qemb_fragment_transform there.
+ * Every call shares the one array and finds the last call's contents in it (nothing needs to start at zero: every
+ * entry the reduction reads is stored earlier in the same call).  Calls that OVERLAP on the GPU -- different streams,
+ * threads -- race on the array: serialise them.  The first call on a device does the one-off set-up (symbol address,
+ * shared-memory attribute, driver entry point, lazy module load): make it before a graph capture, not inside one. */
+int qemb_gram_noalloc(const double *X_dev, int64_t ldx, int64_t naux, int64_t npair, double *G_dev, int64_t ldg,
+                      void *stream);
+int qemb_gram_noalloc_limits(int64_t *max_npair, int64_t *scratch_bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -147,6 +147,8 @@ _SIGS = {
     "qemb_host_alloc": (c_int, [ctypes.POINTER(c_p), c_i64]),
     "qemb_host_free": (c_int, [c_p]),
     "qemb_probe_dmma_tflops": (c_int, [c_p, c_i64, c_i64, c_int, ctypes.POINTER(c_dbl)]),
+    "qemb_gram_noalloc": (c_int, [c_p, c_i64, c_i64, c_i64, c_p, c_i64, c_p]),
+    "qemb_gram_noalloc_limits": (c_int, [ctypes.POINTER(c_i64), ctypes.POINTER(c_i64)]),
 }
 
 

@@ -89,6 +89,11 @@ static int fail(int code, const std::string &msg)
         if (rc__ != QEMB_OK) return rc__;                                                               \
     } while (0)
 
+// for the other translation units of the library (gram_noalloc.cu): same thread-local message, same codes
+namespace qemb {
+int api_fail(int code, const char *msg) { return fail(code, msg ? msg : ""); }
+} // namespace qemb
+
 extern "C" const char *qemb_last_error(void) { return g_err.c_str(); }
 extern "C" const char *qemb_version(void) { return "quemb-b200 0.1 (sm_100a, FP64 DMMA)"; }
 
