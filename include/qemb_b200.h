@@ -158,6 +158,11 @@ int qemb_fragment_get_lists(const qemb_workspace *, int64_t *A_ptr, int64_t *A_i
  * column offsets = running counter over i then mu in A(i) (cpp:467-482).  Result stays on the device
  * inside the workspace. */
 int qemb_fragment_contract_1st(qemb_workspace *, const qemb_tensor *);
+/* (P | mu i) from the caller instead of from K1: the public constructors of SemiSparse3DTensor (pyi:41-58,
+ * cpp:308-352) build the K1 result from host data, and contract_with_TA_2nd_to_sym_dense accepts such a tensor.
+ * B_host is naux x n_mu_i column-major (columns in the order of qemb_fragment_set_lists' lists, cpp:467-482), copied
+ * before the call returns; qemb_fragment_contract_2nd / _solve / _gram then run on it. */
+int qemb_fragment_set_B(qemb_workspace *, int64_t naux, const double *B_host, int64_t ld);
 /* K2a, contract_with_TA_2nd_to_sym_dense cpp:560-605: sym[:, T(hi)+lo] = sum_{mu in A(lo)} TA(mu,hi) B[:, off(lo,mu)] */
 int qemb_fragment_contract_2nd(qemb_workspace *);
 /* K2b, eval_via_cholesky step 1 cpp:615: X = L^-1 sym (in place in the workspace) */

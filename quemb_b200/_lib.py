@@ -104,6 +104,7 @@ _SIGS = {
     "qemb_fragment_get_lists": (c_int, [c_p, c_p, c_p]),
     "qemb_fragment_contract_1st": (c_int, [c_p, c_p]),
     "qemb_fragment_contract_2nd": (c_int, [c_p]),
+    "qemb_fragment_set_B": (c_int, [c_p, c_i64, c_p, c_i64]),
     "qemb_fragment_solve": (c_int, [c_p, c_p]),
     "qemb_fragment_gram": (c_int, [c_p]),
     "qemb_fragment_get_B": (c_int, [c_p, c_p, c_i64]),

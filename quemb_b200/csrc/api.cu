@@ -1965,6 +1965,34 @@ extern "C" int qemb_fragment_contract_1st(qemb_workspace *w, const qemb_tensor *
     return contract_1st(w, t, 0, -1);
 }
 
+// (P | mu i) supplied by the caller instead of computed by K1: the reference lets a user construct a SemiSparse3DTensor
+// from host data (pyi:41-58, cpp:308-352) and hand it to contract_with_TA_2nd_to_sym_dense (cpp:560-605)
+extern "C" int qemb_fragment_set_B(qemb_workspace *w, int64_t naux, const double *B_host, int64_t ld)
+{
+    REQ(w && w->started, "null argument or no fragment planned (qemb_fragment_set_lists comes first)");
+    REQ(naux > 0 && naux < ((int64_t)1 << 31) - 128, "naux out of range");
+    Slot &s = w->slot[w->cur];
+    REQ(s.nA == 0 || (B_host && ld >= naux), "null B or ld < naux");
+    DeviceGuard g(w->ctx->device);
+    w->naux = naux;
+    w->mrows = round_up(naux, 16);
+    w->ldp = round_up(naux, 128);
+    const size_t bytes = (size_t)w->ldp * (size_t)std::max<int64_t>(s.nA, 1) * 8;
+    TRY(w->Bint.reserve(bytes));
+    cudaStream_t cs = w->compute;
+    CU(cudaStreamWaitEvent(cs, s.ta_ready, 0)); // K2a reads TA; K1, which normally orders this, does not run
+    CU(cudaMemsetAsync(w->Bint.p, 0, bytes, cs)); // rows [naux, ldp) must read as zero
+    if (s.nA > 0) {
+        CU(cudaMemcpy2DAsync(w->Bint.p, (size_t)w->ldp * 8, B_host, (size_t)ld * 8, (size_t)naux * 8, (size_t)s.nA,
+                             cudaMemcpyHostToDevice, cs));
+        w->ctx->h2d_bytes += naux * s.nA * 8;
+    }
+    CU(cudaStreamSynchronize(cs)); // B_host may be pageable and is the caller's again when this returns
+    w->have_B = true;
+    w->have_sym = w->solved = w->have_G = false;
+    return QEMB_OK;
+}
+
 extern "C" int qemb_fragment_contract_2nd(qemb_workspace *w)
 {
     REQ(w && w->started, "null argument or no fragment planned");

@@ -195,6 +195,9 @@ class Workspace:
         check(lib().qemb_workspace_create(self.ctx._h, ctypes.byref(h)))
         self._h = h
         self.last_ticket = -1
+        # identity of the K1 result the workspace currently holds (SemiSparse3DTensor._resident); every call that plans
+        # another fragment here drops it
+        self._k1_token: object | None = None
         self._finalizer = weakref.finalize(self, lib().qemb_workspace_destroy, h)
 
     def wait_output(self, ticket: int) -> None:
@@ -637,15 +640,83 @@ class SemiSparseSym3DTensor:
 
 
 class SemiSparse3DTensor:
-    """(P | mu i) after the first contraction.  The data live in the workspace that produced them
-    (device resident); ``dense_data`` downloads them."""
+    """(P | mu i), the result of the first contraction (``cpp:300-437``, ``pyi:38-75``).
 
-    def __init__(self, ws: Workspace, shape, AO_reachable_by_MO, TA: np.ndarray):
-        self._ws = ws
+    Two kinds of instances behave alike:
+
+    * what :func:`contract_with_TA_1st` returns: the data live in the workspace that produced them (device
+      resident) and :attr:`dense_data` downloads them;
+    * what the reference's three public constructors build from host data (``cpp:303-347``, ``pyi:41-58``):
+      ``SemiSparse3DTensor(shape, AO_reachable_by_MO)`` (NaN-filled like ``cpp:346``),
+      ``SemiSparse3DTensor(dense_data, shape, AO_reachable_by_MO)`` and the 5-argument expert form; the data stay on
+      the host until :func:`contract_with_TA_2nd_to_sym_dense` uploads them (``qemb_fragment_set_B``).
+
+    ``mut_dense_data`` is a writable host view in both cases; a K1 result that was written through it is treated like
+    host data from then on.
+    """
+
+    def __init__(self, *args, ctx: Context | None = None) -> None:
+        data = with_off = offsets = None
+        if len(args) == 2:
+            shape, lists = args
+        elif len(args) == 3:
+            data, shape, lists = args
+        elif len(args) == 5:
+            data, shape, lists, with_off, offsets = args
+        else:
+            raise TypeError("SemiSparse3DTensor(shape, AO_reachable_by_MO), (dense_data, shape, AO_reachable_by_MO) or "
+                            "(dense_data, shape, AO_reachable_by_MO, AO_reachable_by_MO_with_offsets, offsets)")
+        self._shape = tuple(int(x) for x in shape)
+        if len(self._shape) != 3:
+            raise TypeError("shape must be (naux, nao, nmo)")
+        self._lists = [list(map(int, x)) for x in lists]
+        self._n = sum(len(x) for x in self._lists)
+        self._ctx = ctx
+        self._ws: Workspace | None = None
+        self._token = None
+        self._TA = None
+        if with_off is None:
+            # build_offsets_and_pairs, cpp:405-423: running counter over i then mu; NOTE the key of the offsets map
+            # is ravel_Fortran(i_MO, mu, nao) = i + mu * nao here, while K1 files mu + i * nao (cpp:515)
+            self._with_off = get_AO_reachable_by_MO_with_offset(self._lists)
+            nao = self._shape[1]
+            self._offsets = {i + mu * nao: off for i, row in enumerate(self._with_off) for off, mu in row}
+        else:
+            self._with_off = [[(int(o), int(mu)) for o, mu in row] for row in with_off]
+            self._offsets = {int(k): int(v) for k, v in dict(offsets).items()}
+        if data is None:
+            self._host = np.full((self._shape[0], self._n), np.nan, order="F")  # cpp:346
+        else:
+            self._host = np.array(data, dtype=np.float64, order="F")  # pybind11 copies numpy -> Eigen (SURVEY 8b)
+            if self._host.ndim != 2:
+                raise TypeError("dense_data must be a matrix")
+
+    @classmethod
+    def _from_workspace(cls, ws: Workspace, shape, AO_reachable_by_MO, TA: np.ndarray) -> "SemiSparse3DTensor":
+        """The K1 result left in ``ws`` (:func:`contract_with_TA_1st`)."""
+        self = cls.__new__(cls)
         self._shape = tuple(int(x) for x in shape)
         self._lists = [list(map(int, x)) for x in AO_reachable_by_MO]
-        self._TA = TA
         self._n = sum(len(x) for x in self._lists)
+        self._ctx = ws.ctx
+        self._ws = ws
+        self._token = ws._k1_token = object()
+        self._TA = TA
+        self._with_off = get_AO_reachable_by_MO_with_offset(self._lists)
+        nao = self._shape[1]
+        self._offsets = {mu + i * nao: off for i, row in enumerate(self._with_off) for off, mu in row}  # cpp:513-518
+        self._host = None
+        return self
+
+    def _resident(self) -> bool:
+        """True while the workspace still holds this tensor's columns."""
+        return self._ws is not None and self._ws._k1_token is self._token
+
+    def __repr__(self) -> str:  # cpp:386-398
+        naux, nao, nmo = self._shape
+        nz, size = self.nonzero_size, self.size
+        return (f"Semi-sparse 3D tensor, shape=({naux}, {nao}, {nmo}), n non-zero, unique elements = {nz}, "
+                f"n dense elements = {size},\ncompression (compared to dense storage) = {100.0 * nz / max(size, 1):g}% \n")
 
     @property
     def shape(self):
@@ -657,6 +728,8 @@ class SemiSparse3DTensor:
 
     @property
     def nonzero_size(self) -> int:
+        if self._host is not None:
+            return int(self._host.size)  # _dense_data.size(), cpp:381
         return self._shape[0] * self._n
 
     @property
@@ -665,27 +738,44 @@ class SemiSparse3DTensor:
 
     @property
     def AO_reachable_by_MO_with_offsets(self):
-        return get_AO_reachable_by_MO_with_offset(self._lists)
+        return self._with_off
 
     @property
     def offsets(self) -> dict[int, int]:
-        nao = self._shape[1]
-        out = {}
-        for i, row in enumerate(self.AO_reachable_by_MO_with_offsets):
-            for off, mu in row:
-                out[mu + i * nao] = off  # ravel_Fortran(mu, i, nao), cpp:513-518
-        return out
+        return self._offsets
 
-    @property
-    def dense_data(self) -> np.ndarray:
+    def _download(self) -> np.ndarray:
+        if not self._resident():
+            raise _lib.QembError("the workspace that held this (P | mu i) has been reused for another fragment; "
+                                 "read dense_data before the next fragment, or give each tensor its own Workspace")
         out = np.zeros((self._shape[0], max(self._n, 1)), order="F")
         if self._n:
             check(lib().qemb_fragment_get_B(self._ws._h, ptr(out), c_i64(self._shape[0])))
         return out[:, : self._n]
 
+    @property
+    def dense_data(self) -> np.ndarray:
+        if self._host is not None:
+            v = self._host.view()
+            v.flags.writeable = False
+            return v
+        return self._download()
+
+    @property
+    def mut_dense_data(self) -> np.ndarray:
+        """Writable view (``pyi:66-67``, ``cpp:363-366``).  For a K1 result the columns are brought to the host first
+        and the tensor is host data from then on (the next K2a uploads whatever was written)."""
+        if self._host is None:
+            self._host = np.asfortranarray(self._download())
+            self._ws = self._token = None
+        return self._host
+
     def __getitem__(self, key):
-        mu, i = key
-        return self.dense_data[:, self.offsets[mu + i * self._shape[1]]]
+        a, b = key
+        k = int(a) + int(b) * self._shape[1]  # get_aux_vector: _offsets.at(ravel_Fortran(mu, i, nao)), cpp:383-387
+        if k not in self._offsets:
+            raise IndexError(f"({a}, {b}) is not stored in this tensor")  # std::out_of_range
+        return self.dense_data[:, self._offsets[k]]
 
 
 # ---------------------------------------------------------------------------
@@ -725,6 +815,7 @@ def get_AO_per_MO(TA, S_abs, epsilon: float, *, ctx: Context | None = None, ws: 
     TA = _f64(TA, "TA")
     sc = _screen_for(S_abs, ctx)
     n = c_i64()
+    ws._k1_token = None
     check(lib().qemb_fragment_screen(ws._h, sc._h, ptr(TA), c_i64(TA.strides[1] // 8 if TA.shape[1] > 1 else TA.shape[0]),
                                      c_i64(TA.shape[0]), c_i64(TA.shape[1]), c_dbl(epsilon), ctypes.byref(n)))
     return ws.lists(TA.shape[1])
@@ -745,14 +836,41 @@ def contract_with_TA_1st(TA, int_P_mu_nu: SemiSparseSym3DTensor, AO_by_MO, *, ws
                                         ptr(aptr), ptr(aidx)))
     check(lib().qemb_fragment_contract_1st(ws._h, int_P_mu_nu._h))
     naux = int_P_mu_nu.shape[0]
-    return SemiSparse3DTensor(ws, (naux, TA.shape[0], TA.shape[1]), AO_by_MO, TA)
+    return SemiSparse3DTensor._from_workspace(ws, (naux, TA.shape[0], TA.shape[1]), AO_by_MO, TA)
 
 
-def contract_with_TA_2nd_to_sym_dense(int_mu_i_P: SemiSparse3DTensor, TA) -> np.ndarray:
-    """K2a, ``cpp:560-605``: (P | ij), pair column T(max)+min, lists of min / TA column of max."""
-    ws = int_mu_i_P._ws
+def contract_with_TA_2nd_to_sym_dense(int_mu_i_P: SemiSparse3DTensor, TA, *, ws: Workspace | None = None) -> np.ndarray:
+    """K2a, ``cpp:560-605``: (P | ij), pair column T(max)+min, lists of min / TA column of max.
+
+    A tensor that :func:`contract_with_TA_1st` left on the device is contracted where it lives when ``TA`` is the
+    matrix K1 ran with; a tensor built from host data (the reference's public constructors, ``mut_dense_data``), or a
+    different ``TA``, goes through ``qemb_fragment_set_lists`` + ``qemb_fragment_set_B`` first."""
+    naux, nao, nmo = int_mu_i_P.shape
+    TA = _f64(TA, "TA")
+    if TA.shape != (nao, nmo):
+        raise _lib.QembError(f"TA has shape {TA.shape}, the tensor wants {(nao, nmo)}")  # assert cpp:576-577
+    same_TA = int_mu_i_P._TA is not None and (TA is int_mu_i_P._TA or np.array_equal(TA, int_mu_i_P._TA))
+    if int_mu_i_P._resident() and same_TA:
+        ws = int_mu_i_P._ws
+    else:
+        host = int_mu_i_P.dense_data  # downloads a K1 result whose TA differs (raises if the workspace moved on)
+        ws = ws or default_workspace(int_mu_i_P._ctx or default_context())
+        with_off = int_mu_i_P.AO_reachable_by_MO_with_offsets
+        lists = [[mu for _, mu in row] for row in with_off]
+        cols = np.fromiter((off for row in with_off for off, _ in row), dtype=np.int64)
+        if cols.size and (cols.min() < 0 or cols.max() >= host.shape[1]):
+            raise IndexError("an offset of AO_reachable_by_MO_with_offsets lies outside dense_data")
+        if host.shape[0] != naux:
+            raise _lib.QembError("dense_data has the wrong number of rows")
+        # the library's column order is the running counter over (i, mu) (cpp:467-482); the expert constructor may
+        # carry any offsets
+        B = host if np.array_equal(cols, np.arange(cols.size)) and host.shape[1] == cols.size else host[:, cols]
+        B = np.asfortranarray(B)
+        aptr, aidx = to_csr(lists)
+        ws._k1_token = None
+        check(lib().qemb_fragment_set_lists(ws._h, ptr(TA), c_i64(_ld(TA)), c_i64(nao), c_i64(nmo), ptr(aptr), ptr(aidx)))
+        check(lib().qemb_fragment_set_B(ws._h, c_i64(naux), ptr(B) if B.size else None, c_i64(max(naux, 1))))
     check(lib().qemb_fragment_contract_2nd(ws._h))
-    naux, _, nmo = int_mu_i_P.shape
     out = np.empty((naux, nmo * (nmo + 1) // 2), order="F")
     check(lib().qemb_fragment_get_sym(ws._h, ptr(out), c_i64(naux)))
     return out
@@ -791,6 +909,7 @@ def transform_integral(
     if not (out.flags.f_contiguous or out.flags.c_contiguous):
         raise _lib.QembError("out must be contiguous")  # G is symmetric: C and F order coincide
     ticket = c_i64()
+    ws._k1_token = None
     check(lib().qemb_fragment_transform(
         ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
         c_i64(nmo), c_dbl(MO_coeff_epsilon), c_i64(p_range[0]), c_i64(p_range[1]), ptr(out), c_i64(ld_out), c_int(0),
@@ -821,6 +940,7 @@ def transform_integral_device(
     int_P_mu_nu._flush()
     sc = _screen_for(S_abs, ctx)
     m = None if (L_PQ is None) else _metric_for(L_PQ, ctx)
+    ws._k1_token = None
     check(lib().qemb_fragment_transform(
         ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
         c_i64(TA.shape[1]), c_dbl(MO_coeff_epsilon), c_i64(p_range[0]), c_i64(p_range[1]), c_p(out_dev_ptr),
@@ -837,6 +957,7 @@ def transform_integral_resident(int_P_mu_nu: SemiSparseSym3DTensor, TA, S_abs, L
     int_P_mu_nu._flush()
     sc = _screen_for(S_abs, ctx)
     m = None if (L_PQ is None) else _metric_for(L_PQ, ctx)
+    ws._k1_token = None
     check(lib().qemb_fragment_transform(
         ws._h, int_P_mu_nu._h, None if m is None else m._h, sc._h, ptr(TA), c_i64(_ld(TA)), c_i64(TA.shape[0]),
         c_i64(TA.shape[1]), c_dbl(MO_coeff_epsilon), c_i64(0), c_i64(-1), None, c_i64(0), c_int(0), None))

@@ -73,6 +73,52 @@ def test_steps_match_reference_golden(q, name):
 
 
 @pytest.mark.parametrize("name", CASES)
+def test_K2a_on_caller_built_tensors_matches_reference_golden(q, name):
+    """The reference's public SemiSparse3DTensor constructors (pyi:41-58) and mut_dense_data feed
+    contract_with_TA_2nd_to_sym_dense from HOST data (qemb_fragment_set_B); expected values: the reference's own `sym`."""
+    g = Golden(name)
+    T = _tensor(q, g)
+    for f in range(g.n_frag):
+        fr = g.frag(f)
+        A, TA, Bref = [a.tolist() for a in fr["A"]], fr["TA"], np.asfortranarray(fr["B"])
+        shape = (g.naux, g.nao, TA.shape[1])
+        # (dense_data, shape, lists)
+        sym = q.contract_with_TA_2nd_to_sym_dense(q.SemiSparse3DTensor(Bref, shape, A), TA)
+        assert np.abs(sym - fr["sym"]).max() <= TOL_STEP
+        # (shape, lists) filled through mut_dense_data
+        t = q.SemiSparse3DTensor(shape, A)
+        assert np.isnan(t.dense_data).all() or t.nonzero_size == 0
+        t.mut_dense_data[...] = Bref
+        assert np.array_equal(q.contract_with_TA_2nd_to_sym_dense(t, TA), sym)
+        # expert form with permuted columns
+        n = Bref.shape[1]
+        perm = np.random.default_rng(f).permutation(n)
+        with_off, k = [], 0
+        for row in A:
+            with_off.append([(int(perm[k + j]), mu) for j, mu in enumerate(row)])
+            k += len(row)
+        D = np.empty_like(Bref)
+        D[:, perm] = Bref
+        e = q.SemiSparse3DTensor(D, shape, A, with_off, {mu + i * g.nao: o for i, r in enumerate(with_off) for o, mu in r})
+        assert np.array_equal(q.contract_with_TA_2nd_to_sym_dense(e, TA), sym)
+        # a K1 result: written through mut_dense_data (scaled by 2), and contracted with ANOTHER TA than K1 ran with
+        B = q.contract_with_TA_1st(TA, T, A)
+        assert B._resident()
+        TA2 = np.asfortranarray(TA * 0.5)
+        sym_half = q.contract_with_TA_2nd_to_sym_dense(B, TA2)  # same lists, other coefficients: host route
+        assert np.abs(sym_half - 0.5 * fr["sym"]).max() <= TOL_STEP
+        B = q.contract_with_TA_1st(TA, T, A)
+        B.mut_dense_data[...] *= 2.0
+        assert not B._resident()
+        assert np.abs(q.contract_with_TA_2nd_to_sym_dense(B, TA) - 2.0 * fr["sym"]).max() <= 2 * TOL_STEP
+        # a tensor whose workspace has moved on says so instead of returning another fragment's columns
+        B = q.contract_with_TA_1st(TA, T, A)
+        q.get_AO_per_MO(TA, g.S_abs, g.eps)
+        with pytest.raises(_lib.QembError, match="reused"):
+            B.dense_data
+
+
+@pytest.mark.parametrize("name", CASES)
 def test_whitened_tensor_matches_reference_golden(q, name):
     """Design option O1: L^-1 applied to (P|mu nu) once instead of per fragment."""
     g = Golden(name)
