@@ -593,6 +593,13 @@ class SemiSparseSym3DTensor:
         check(lib().qemb_tensor_is_whitened(self._h, ctypes.byref(f)))
         return bool(f.value)
 
+    def __repr__(self) -> str:  # cpp:214-225
+        naux, nao1, nao2 = self._shape
+        nz, size = self.nonzero_size, self.size
+        return (f"Semi-sparse symmetric 3D tensor, shape=({naux}, {nao1}, {nao2}), n non-zero, unique elements = {nz}, "
+                f"n dense elements = {size},\ncompression (compared to non-symmetric, dense storage) = "
+                f"{100.0 * nz / max(size, 1):g}% \n")
+
     # -- index structures -------------------------------------------------------
     @property
     def shape(self) -> tuple[int, int, int]:
