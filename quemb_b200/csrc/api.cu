@@ -475,6 +475,17 @@ extern "C" int qemb_ctx_create(int device, qemb_ctx **out)
         const int n = std::atoi(e);
         c->k3_slices = (n >= 5 && n <= 8) ? n : 0;
     }
+    // Experiment knob, default untouched: an L2 set-aside for persisting lines, which the evict_last loads
+    // of K3's row panels then compete for.  The device limit is process-wide for this GPU.
+    if (const char *e = std::getenv("QEMB_L2_PERSIST_MB")) {
+        size_t want = (size_t)std::max(0, std::atoi(e)) << 20;
+        if (want > (size_t)prop.persistingL2CacheMaxSize) want = (size_t)prop.persistingL2CacheMaxSize;
+        const cudaError_t r = cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+        if (r != cudaSuccess) (void)cudaGetLastError();
+        std::fprintf(stderr, "[qemb] QEMB_L2_PERSIST_MB: persisting L2 set-aside %zu MB of at most %d MB (%s), L2 %d MB\n",
+                     want >> 20, prop.persistingL2CacheMaxSize >> 20, r == cudaSuccess ? "set" : cudaGetErrorString(r),
+                     prop.l2CacheSize >> 20);
+    }
     CU(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->prep, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));

@@ -106,7 +106,8 @@ struct GramTmaParams {
     // 1: the lower tiles are ADDED (system-scope red.add.f64) into G, which may live in a peer GPU's memory (NVLink):
     // the reduce-sum of an aux-sharded fragment happens in the epilogue, tile by tile, while the other tiles compute
     int accumulate;
-    int hint; // L2 hints of the operand loads: 0 none, 1 row panel evict_last, 2 + column panel evict_first
+    int hint; // L2 hints of the operand loads: bits 0-1: 0 none, 1 row panel evict_last, 2 + column panel evict_first;
+              // bit 2 (value 4): alternate the k direction from tile to tile
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -141,15 +142,22 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramTmaParams p)
                 const int2 tt = p.tiles[w / p.nsplit];
                 const int m0 = tt.x * TM, n0 = tt.y * TN;
                 const int kbeg = (w % p.nsplit) * p.kchunk, kend = min(p.ktiles, kbeg + p.kchunk);
-                for (int kt = kbeg; kt < kend; ++kt) {
+                // hint bit 2 (experiment, off by default): every other tile of a CTA walks k downwards.  The CTAs of a
+                // wave advance through k together, so when a wave ends L2 holds the k TAILS of its panels; a next wave
+                // that starts at k = 0 finds none of them (cyclic LRU thrash), one that starts at the tail re-uses
+                // the band's row panels as far as they survived.  Only the producer's coordinates change: the
+                // consumers accumulate stages in arrival order (sum order of such a tile reversed, still deterministic).
+                const bool rev = (p.hint & 4) && (((w - (int)blockIdx.x) / (int)gridDim.x) & 1);
+                for (int kq = kbeg; kq < kend; ++kq) {
+                    const int kt = rev ? kend - 1 - (kq - kbeg) : kq;
                     mbar_wait(&empty[s], phase ^ 1);
                     mbar_expect_tx(&full[s], STAGE_BYTES);
                     uint8_t *As = smem + s * STAGE_BYTES;
-                    if (p.hint >= 1)
+                    if (p.hint & 3)
                         tma_load_2d_hint(As, &tmap, kt * BK, m0, &full[s], pol_last);
                     else
                         tma_load_2d(As, &tmap, kt * BK, m0, &full[s]);
-                    if (p.hint >= 2)
+                    if ((p.hint & 3) >= 2)
                         tma_load_2d_hint(As + TILE_BYTES, &tmap, kt * BK, n0, &full[s], pol_first);
                     else
                         tma_load_2d(As + TILE_BYTES, &tmap, kt * BK, n0, &full[s]);
