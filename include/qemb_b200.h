@@ -250,6 +250,12 @@ int qemb_ctx_autotune_copy_alone(const qemb_ctx *, double *d2h_alone_gbs);
  * split -- as four back-to-back deliveries of a 0.5 GB test matrix each through the real output path and keeps the
  * fastest (the model's choice stands if the trials cannot run).  Seconds per candidate, -1 = not run: */
 int qemb_ctx_autotune_trials(const qemb_ctx *, double *secs3);
+/* Trial times within 5 % of the fastest are a tie, broken by the rate model (2 / P0 for full squares,
+ * max((1 + f) / P, (1 - f) / M) for a split f): the trial matrix is a tenth of a fragment and one box tied two modes whose
+ * builds differ by 20 %.  qemb_autotune_pick is that rule as a host-only test hook: candidates 0 full squares, 1 pure
+ * triangle, 2 split with upper3[2] of the upper triangle over PCIe; secs <= 0 = not run; *pick = -1 if none ran. */
+int qemb_autotune_pick(const double *secs3, const double *upper3, double d2h_alone_gbs, double d2h_gbs, double mirror_gbs,
+                       int *pick);
 
 /* OPT-IN variant of K3 (G = X^T X, cpp:620): 0 = FP64 tensor path (default, the parity reference), 5 .. 8 = error-free
  * split of X into that many 8-bit integer slices (balanced base-256 digits of each column rounded below its exponent)

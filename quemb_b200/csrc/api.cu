@@ -2472,6 +2472,41 @@ extern "C" int qemb_device_to_host(qemb_ctx *c, void *host, const void *dev, int
 // the real machinery (column groups on the copy stream, completion callbacks, mirror tasks on the host pool, two host
 // buffers in rotation) and the fastest wins.  All ranks of a node call this at the same moment and walk the candidates
 // in the same order, so every candidate is timed under the contention it would see.
+// Which candidate wins -- 0 full squares, 1 pure triangle, 2 a split sending the fraction upper[2] of the upper triangle
+// over PCIe -- given the seconds their trial deliveries took (<= 0: not run) and the measured rates.  A trial is four
+// deliveries of a matrix a tenth of a fragment: candidates it puts within 5 % of the fastest are a TIE (one N = 1 box:
+// 0.03809 s for full squares, 0.03829 s for the triangle; the builds took 2.81 s and 2.30 s).  Ties go to the candidate
+// the rate model makes cheapest per byte of upper triangle: 2 / P0 for full squares, max((1 + f) / P, (1 - f) / M) for
+// a split f (f = 0: the pure triangle).  On every box recorded under profiles/ this is the mode that won the build
+// (tests/test_driver_host.py).  Returns -1 when nothing was timed.
+static int autotune_pick(const double *secs, const double *upper, double P0, double P, double M)
+{
+    int fastest = -1;
+    for (int k = 0; k < 3; ++k)
+        if (secs[k] > 0 && (fastest < 0 || secs[k] < secs[fastest])) fastest = k;
+    if (fastest < 0 || !(P0 > 0 && P > 0 && M > 0)) return fastest;
+    int pick = -1;
+    double best_cost = 0.0;
+    for (int k = 0; k < 3; ++k) {
+        if (secs[k] <= 0 || secs[k] > 1.05 * secs[fastest]) continue;
+        const double cost = k == 0 ? 2.0 / P0 : std::max((1.0 + upper[k]) / P, (1.0 - upper[k]) / M);
+        if (pick < 0 || cost < best_cost) {
+            pick = k;
+            best_cost = cost;
+        }
+    }
+    return pick;
+}
+
+// test hook for the rule above (host only, no device): secs3 / upper3 = the three candidates
+extern "C" int qemb_autotune_pick(const double *secs3, const double *upper3, double d2h_alone_gbs, double d2h_gbs,
+                                  double mirror_gbs, int *pick)
+{
+    REQ(secs3 && upper3 && pick, "null argument");
+    *pick = autotune_pick(secs3, upper3, d2h_alone_gbs, d2h_gbs, mirror_gbs);
+    return QEMB_OK;
+}
+
 extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mirror_gbs, double *upper_fraction_pcie)
 {
     double P = 0, M = 0, f = 0;
@@ -2537,6 +2572,15 @@ extern "C" int qemb_ctx_autotune_output(qemb_ctx *c, double *d2h_gbs, double *mi
     int best = -1;
     for (int k = 0; k < ncand; ++k)
         if (cand[k].secs > 0 && (best < 0 || cand[k].secs < cand[best].secs)) best = k;
+    if (best >= 0) {
+        double secs[3], upper[3];
+        for (int k = 0; k < 3; ++k) {
+            secs[k] = k < ncand ? cand[k].secs : -1.0;
+            upper[k] = cand[k].upper;
+        }
+        const int pick = autotune_pick(secs, upper, c->tune_p0, P, M);
+        if (pick >= 0) best = pick;
+    }
     cleanup();
     if (best < 0) { // nothing could be timed: keep the model's choice
         (void)cudaGetLastError();

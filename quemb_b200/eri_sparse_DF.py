@@ -100,8 +100,15 @@ class Context:
         check(lib().qemb_ctx_autotune_copy_alone(self._h, ctypes.byref(p0)))
         t = (c_dbl * 3)()
         check(lib().qemb_ctx_autotune_trials(self._h, t))
+        trials = [float(x) for x in t]
+        # which candidate the chosen mode is (0 full squares, 1 pure triangle, 2 the model's split) and whether the trials
+        # alone decided: candidates within 5 % of the fastest trial are a tie that the rate model breaks
+        chosen = 0 if f.value >= 1.0 else (1 if f.value <= 0.0 else 2)
+        ran = [k for k, x in enumerate(trials) if x > 0]
+        fastest = min(ran, key=lambda k: trials[k]) if ran else None
         return {"d2h_alone_gbs": p0.value, "d2h_gbs": p.value, "mirror_gbs": m.value, "upper_fraction_over_pcie": f.value,
-                "trial_s_full_triangle_split": [float(x) for x in t]}
+                "trial_s_full_triangle_split": trials,
+                "decided_by": "model" if fastest is None else ("trials" if fastest == chosen else "model (trials within 5 %)")}
 
     def set_k3_int8_slices(self, slices: int) -> None:
         """Opt-in K3 on the int8 tensor cores (0 = FP64 path, the default and the parity reference; 5 .. 8 integer

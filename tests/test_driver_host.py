@@ -435,3 +435,54 @@ def test_world_size_2_gloo_distributed_fragment_queue(tmp_path):
         assert len(r0[name]) > len(r1[name])
         merged = [7, 3, 5, 0, 1, 6, 2, 4, 8]
         assert [i for i in merged if i in r0[name]] == r0[name]  # each rank sees its share in queue order
+
+
+# ---- output-mode autotune: the tie-break rule (host only) ---------------------------------------------------------------
+# (box, P0, P, M, trial seconds [full squares, triangle, split], split fraction, mode that won the BUILD on that box)
+_AUTOTUNE_RECORDS = [
+    # profiles/bench_r2l_n1_after_noalloc.json: triangle 12 % ahead in the trials; build 2.09 s
+    ("n1 fast-pcie", 57.22, 51.96, 54.08, [0.037860, 0.033312, -1.0], 0.0, 1),
+    # profiles/bench_r2i_n1_autotune_trials.json
+    ("n1 fast-pcie b", 57.22, 48.32, 62.65, [0.037924, 0.034501, -1.0], 0.0, 1),
+    # profiles/bench_r2k_n1_group256.json / bench_r2j_n1_final.json: PCIe drops to 32-34 GB/s under the mirror; triangle
+    # builds 2.30 s, full squares 2.81 s
+    ("n1 slow-pcie a", 55.66, 32.23, 65.67, [0.039073, 0.037569, -1.0], 0.0, 1),
+    ("n1 slow-pcie b", 55.53, 33.99, 65.68, [0.040409, 0.039709, -1.0], 0.0, 1),
+    # profiles/bench_r2m_n1_trial_tie.json: the trials TIE with full squares 0.5 % ahead -> 2.91 s instead of 2.30 s
+    ("n1 slow-pcie tie", 54.92, 32.73, 63.53, [0.038093, 0.038290, -1.0], 0.0, 1),
+    # profiles/bench_r2i_n2_autotune_trials.json, both ranks: the model alone wanted the split, which is 11 % behind in
+    # the trials; full squares build 1.41 s against 1.97 s for the triangle
+    ("n2 rank0", 56.95, 41.52, 25.62, [0.038626, 0.039250, 0.043005], 0.237, 0),
+    ("n2 rank1", 56.77, 42.22, 23.42, [0.038131, 0.040757, 0.043655], 0.287, 0),
+]
+
+
+@pytest.mark.parametrize("rec", _AUTOTUNE_RECORDS, ids=[r[0] for r in _AUTOTUNE_RECORDS])
+def test_autotune_pick_chooses_the_mode_that_won_the_build(rec):
+    import ctypes
+
+    from quemb_b200 import _lib
+
+    _, p0, p, m, secs, f, want = rec
+    pick = ctypes.c_int(-7)
+    a, u = (ctypes.c_double * 3)(*secs), (ctypes.c_double * 3)(1.0, 0.0, f)
+    _lib.check(_lib.lib().qemb_autotune_pick(a, u, p0, p, m, ctypes.byref(pick)))
+    assert pick.value == want
+
+
+def test_autotune_pick_edge_cases():
+    import ctypes
+
+    from quemb_b200 import _lib
+
+    def pick(secs, f=0.0, rates=(55.0, 40.0, 40.0)):
+        out = ctypes.c_int(-7)
+        _lib.check(_lib.lib().qemb_autotune_pick((ctypes.c_double * 3)(*secs), (ctypes.c_double * 3)(1.0, 0.0, f), *rates,
+                                                 ctypes.byref(out)))
+        return out.value
+
+    assert pick([-1.0, -1.0, -1.0]) == -1                      # nothing ran: the caller keeps the model's choice
+    assert pick([0.05, -1.0, -1.0]) == 0                       # a single candidate
+    assert pick([0.030, 0.040, -1.0]) == 0                     # decisive trials beat the model (which prefers 1 here)
+    assert pick([0.040, 0.030, 0.0301], f=0.3, rates=(55.0, 40.0, 20.0)) == 2  # tie 1 / 2: the model prefers the split
+    assert pick([0.040, 0.041, -1.0], rates=(0.0, 0.0, 0.0)) == 0  # no rates: fastest trial
