@@ -109,3 +109,25 @@ def test_log_level_default_and_roundtrip_in_a_fresh_process():
             % str(_lib.ROOT))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.split() == ["40", "20", "40"], r.stderr
+
+
+def test_gram_noalloc_argument_checks_need_no_device(L):
+    """``qemb_gram_noalloc`` rejects bad arguments -- above all sizes beyond its fixed scratch array -- before it touches
+    CUDA, and on a box without a GPU a well-formed call fails loudly instead of falling back to anything."""
+    i64, vp = ctypes.c_int64, ctypes.c_void_p
+    mx, sb = i64(), i64()
+    assert L.qemb_gram_noalloc_limits(ctypes.byref(mx), ctypes.byref(sb)) == 0
+    assert mx.value == 2048 and sb.value == 32 << 20 and 8 * mx.value ** 2 <= sb.value
+    fake = vp(4096)  # never dereferenced on these paths
+    assert L.qemb_gram_noalloc(vp(None), i64(16), i64(16), i64(8), fake, i64(8), vp(None)) == _lib.QEMB_EINVAL
+    assert b"null" in L.qemb_last_error()
+    assert L.qemb_gram_noalloc(fake, i64(16), i64(16), i64(mx.value + 1), fake, i64(mx.value + 1), vp(None)) == _lib.QEMB_EINVAL
+    msg = L.qemb_last_error().decode()
+    assert "exceeds the maximum of 2048" in msg and "32 MiB" in msg
+    assert L.qemb_gram_noalloc(fake, i64(15), i64(16), i64(8), fake, i64(8), vp(None)) == _lib.QEMB_EINVAL   # ldx < naux
+    assert L.qemb_gram_noalloc(fake, i64(17), i64(16), i64(8), fake, i64(8), vp(None)) == _lib.QEMB_EINVAL   # odd ldx
+    assert L.qemb_gram_noalloc(fake, i64(16), i64(16), i64(8), fake, i64(7), vp(None)) == _lib.QEMB_EINVAL   # ldg < npair
+    assert L.qemb_gram_noalloc(fake, i64(16), i64(0), i64(8), fake, i64(8), vp(None)) == _lib.QEMB_EINVAL    # naux < 1
+    if _lib.device_count() == 0:
+        rc = L.qemb_gram_noalloc(fake, i64(16), i64(16), i64(8), fake, i64(8), vp(None))
+        assert rc in (_lib.QEMB_ENODEV, _lib.QEMB_ECUDA) and L.qemb_last_error()
