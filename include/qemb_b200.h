@@ -278,6 +278,13 @@ int qemb_fragment_k3_choice(const qemb_workspace *, int *slices, int *max_expo);
  * (expo[c]; a column holding NaN / Inf gets the poison value -2^30 and zero digits) and the digits
  * D[(c * slices + a) * nrows + p].  Test hook for the CPU suite; no reference counterpart, not on the product path. */
 int qemb_k3_int8_slice_host(const double *X, int64_t ldx, int64_t nrows, int64_t ncols, int slices, int8_t *D, int *expo);
+/* Host-only test hooks (no reference counterpart, not on the product path) for the schedules the persistent kernels
+ * walk: the lower-triangular tile order of K3 (2 ints per tile into ti_tj, nt (nt + 1) / 2 tiles; returns the count),
+ * the k splits of a small K3 (launch_gram's nsplit and 16-row k tiles per split), and the order in which the
+ * gather-GEMM tiles of given costs are dealt to `num_sms` persistent CTAs (order = a permutation of 0 .. n-1). */
+int64_t qemb_test_gram_tiles(int nt, int32_t *ti_tj);
+int qemb_test_gram_splits(int ntiles, int ktiles, int num_sms, int *nsplit, int *kchunk);
+int qemb_test_balance_tiles(int64_t n, const float *cost, int num_sms, int32_t *order);
 /* host DRAM bandwidth seen by the library's host threads: non-temporal fill of `bytes` (write_gbs) and parallel memcpy
  * of bytes/2 (copy_gbs = bytes copied per second); best of 3.  Denominator of bench.py's e2e.host_roofline_frac. */
 int qemb_host_bandwidth(int64_t bytes, double *write_gbs, double *copy_gbs);

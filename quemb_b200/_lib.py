@@ -69,6 +69,9 @@ _SIGS = {
     "qemb_ctx_autotune_output": (c_int, [c_p, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
     "qemb_ctx_autotune_copy_alone": (c_int, [c_p, ctypes.POINTER(c_dbl)]),
     "qemb_ctx_autotune_trials": (c_int, [c_p, c_p]),
+    "qemb_test_gram_tiles": (c_i64, [c_int, c_p]),
+    "qemb_test_gram_splits": (c_int, [c_int, c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
+    "qemb_test_balance_tiles": (c_int, [c_i64, c_p, c_int, c_p]),
     "qemb_autotune_pick": (c_int, [c_p, c_p, c_dbl, c_dbl, c_dbl, ctypes.POINTER(c_int)]),
     "qemb_device_count": (c_int, [ctypes.POINTER(c_int)]),
     "qemb_ctx_create": (c_int, [c_int, ctypes.POINTER(c_p)]),

@@ -2498,6 +2498,40 @@ static int autotune_pick(const double *secs, const double *upper, double P0, dou
     return pick;
 }
 
+// test hooks for the host-side schedules of K3 and of the gather GEMMs (host only, no device):
+//   tiles: the lower-triangular tile walk of K3 (bands of QEMB_K3_GROUP row tiles), (ti, tj) pairs, returns the count
+//   splits: k splits of a small K3 and the 16-row k tiles per split launch_gram derives from it
+//   balance: the persistent-kernel order of a gather-GEMM tile list with the given costs (a permutation of 0 .. n-1)
+extern "C" int64_t qemb_test_gram_tiles(int nt, int32_t *ti_tj)
+{
+    if (nt < 0 || (nt > 0 && !ti_tj)) return fail(QEMB_EINVAL, "bad argument");
+    std::vector<int2> h((size_t)nt * (nt + 1) / 2 + 1);
+    const int64_t n = build_gram_tiles(nt, h.data());
+    for (int64_t k = 0; k < n; ++k) {
+        ti_tj[2 * k] = h[(size_t)k].x;
+        ti_tj[2 * k + 1] = h[(size_t)k].y;
+    }
+    return n;
+}
+
+extern "C" int qemb_test_gram_splits(int ntiles, int ktiles, int num_sms, int *nsplit, int *kchunk)
+{
+    REQ(nsplit && kchunk && ntiles >= 0 && ktiles >= 0 && num_sms > 0, "bad argument");
+    *nsplit = gram_splits(ntiles, ktiles, num_sms);
+    *kchunk = (ktiles + *nsplit - 1) / *nsplit;
+    return QEMB_OK;
+}
+
+extern "C" int qemb_test_balance_tiles(int64_t n, const float *cost, int num_sms, int32_t *order)
+{
+    REQ(n >= 0 && num_sms > 0 && (n == 0 || (cost && order)), "bad argument");
+    std::vector<int4> tiles((size_t)n);
+    for (int64_t i = 0; i < n; ++i) tiles[(size_t)i] = make_int4((int)i, 0, 0, 0);
+    balance_tiles(tiles.data(), std::vector<float>(cost, cost + n), n, num_sms);
+    for (int64_t i = 0; i < n; ++i) order[i] = tiles[(size_t)i].x;
+    return QEMB_OK;
+}
+
 // test hook for the rule above (host only, no device): secs3 / upper3 = the three candidates
 extern "C" int qemb_autotune_pick(const double *secs3, const double *upper3, double d2h_alone_gbs, double d2h_gbs,
                                   double mirror_gbs, int *pick)
